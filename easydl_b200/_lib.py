@@ -1,0 +1,82 @@
+"""ctypes binding of libedlsparse.so (include/edlsparse.h).
+
+The product path has no CPU fallback: if the shared library is missing, or a call returns a
+negative code, this module raises.  Build with `python -c "import __graft_entry__ as g;
+g.build()"` or `make -C easydl_b200/csrc`.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libedlsparse.so")
+
+EDL_OPT_ADAGRAD = 0
+EDL_OPT_ADAM = 1
+
+
+class EdlError(RuntimeError):
+    """A libedlsparse call returned a negative EDL_E* code."""
+
+
+class OptParams(C.Structure):
+    _fields_ = [("kind", C.c_int), ("lr", C.c_float), ("eps", C.c_float),
+                ("beta1", C.c_float), ("beta2", C.c_float)]
+
+
+_p = C.c_void_p
+_i64 = C.c_int64
+_sz = C.c_size_t
+_int = C.c_int
+
+# name -> (restype, argtypes); mirrors include/edlsparse.h one to one
+PROTOTYPES = {
+    "edl_version": (_int, []),
+    "edl_last_error_string": (C.c_char_p, []),
+    "edl_init_rows": (_int, [_p, _int, _p, _i64, _i64, C.c_uint64, _p]),
+    "edl_fill_f32": (_int, [_p, _i64, C.c_float, _p]),
+    "edl_unique_workspace_bytes": (_sz, [_i64, _int]),
+    "edl_unique": (_int, [_p, _i64, _p, _p, _int, _int, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "edl_partition_mod_workspace_bytes": (_sz, [_i64, _int]),
+    "edl_partition_mod": (_int, [_p, _i64, _p, _p, _int, _p, _p, _p, _p, _p, _sz, _p]),
+    "edl_gather_keys": (_int, [_p, _int, _p, _i64, _p, _p, _p, _p]),
+    "edl_gather_ids": (_int, [_p, _int, _p, _i64, _p, _int, _p, _p]),
+    "edl_expand": (_int, [_p, _int, _p, _i64, _p, _p]),
+    "edl_compose_index": (_int, [_p, _p, _i64, _p, _p]),
+    "edl_segreduce_workspace_bytes": (_sz, [_i64, _int]),
+    "edl_segreduce": (_int, [_p, _int, _p, _p, _p, _i64, _p, _p, _p, _sz, _p]),
+    "edl_segreduce_update": (_int, [_p, _p, _p, _int, _p, _p, _p, _p, _i64, _p, _p,
+                                    C.POINTER(OptParams), _p, _p, _sz, _p]),
+    "edl_export_workspace_bytes": (_sz, [_i64]),
+    "edl_export_count": (_int, [_p, _i64, _p, _p, _sz, _p]),
+    "edl_export_shard": (_int, [_p, _p, _p, _int, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "edl_import_shard": (_int, [_p, _p, _p, _int, _p, _p, _p, _p, _p, _p, _i64, _p]),
+    "edl_scatter_rows": (_int, [_p, _int, _p, _i64, _p, _p, _p]),
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load the library once; raise loudly when it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise EdlError(
+            f"{LIB_PATH} is missing: the CUDA extension is not built and there is no CPU "
+            "fallback. Run `make -C easydl_b200/csrc` (nvcc, sm_100a).")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)  # AttributeError here == header/library mismatch
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        msg = load().edl_last_error_string().decode("utf-8", "replace")
+        raise EdlError(f"{what} failed with code {rc}: {msg}")

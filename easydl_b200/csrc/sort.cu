@@ -1,0 +1,496 @@
+// A1 dedup/unique and A2 hash-mod partition: LSD radix sort built from one stable
+// counting-sort pass (per-tile histogram -> per-digit row scan -> ranked scatter), then a
+// head-flag scan that emits uniq / inverse / counts / seg_offsets.
+//
+// SPEC: A1 == np.unique(keys, return_inverse, return_counts) on the fused
+// key; A2 == stable partition by (per-table id mod S).  Integer work, bit-exact.
+//
+// Stability inside a tile comes from warp-striped ranking with __match_any_sync: warp w owns
+// 256 consecutive elements, iteration k ranks elements w*256 + k*32 + lane, so rank order ==
+// input order.  Everything for a cfg2 batch (1.7M keys, 28 bits) stays L2-resident.
+#include <algorithm>
+
+#include "edl_common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kItems = 8;
+constexpr int kTile = kThreads * kItems;  // 2048
+constexpr int kWarps = kThreads / 32;
+
+// ------------------------------------------------------------------ loaders / digit functors
+template <typename KeyT>
+struct IdsLoader {  // pass 0 of the sort: fused key formed on the fly, payload = position
+  const int64_t* ids;
+  const int64_t* field_base;
+  int n_fields;
+  __device__ __forceinline__ KeyT key(int64_t j) const {
+    long long k = ids[j];
+    if (field_base) k += field_base[(int)(j % n_fields)];
+    return (KeyT)k;
+  }
+  __device__ __forceinline__ uint32_t val(int64_t j) const { return (uint32_t)j; }
+};
+
+template <typename KeyT>
+struct PairLoader {  // later passes
+  const KeyT* keys;
+  const uint32_t* vals;
+  __device__ __forceinline__ KeyT key(int64_t j) const { return keys[j]; }
+  __device__ __forceinline__ uint32_t val(int64_t j) const { return vals[j]; }
+};
+
+struct KeyIndexLoader {  // partition: int64 key, payload = position
+  const int64_t* keys;
+  __device__ __forceinline__ int64_t key(int64_t j) const { return keys[j]; }
+  __device__ __forceinline__ uint32_t val(int64_t j) const { return (uint32_t)j; }
+};
+
+template <typename KeyT>
+struct BitDigit {
+  int shift;
+  __device__ __forceinline__ unsigned operator()(KeyT k, int64_t) const {
+    return (unsigned)(k >> shift) & 0xFFu;
+  }
+};
+
+struct ArrayDigit {  // partition: digit precomputed by k_shard_digits
+  const uint8_t* dig;
+  __device__ __forceinline__ unsigned operator()(int64_t, int64_t j) const { return dig[j]; }
+};
+
+__device__ __forceinline__ int64_t eff_n(int64_t n, const int32_t* n_dev) {
+  if (n_dev) {
+    int64_t m = *n_dev;
+    return m < n ? m : n;
+  }
+  return n;
+}
+
+// ------------------------------------------------------------------ pass kernel 1: histogram
+template <typename KeyT, typename Loader, typename DigitFn>
+__global__ void __launch_bounds__(kThreads)
+k_hist(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles, uint32_t* __restrict__ hist) {
+  __shared__ unsigned h[256];
+  const int tid = threadIdx.x;
+  h[tid] = 0;
+  __syncthreads();
+  const int64_t ne = eff_n(n, n_dev);
+  const int64_t base = (int64_t)blockIdx.x * kTile;
+#pragma unroll
+  for (int k = 0; k < kItems; ++k) {
+    int64_t j = base + k * kThreads + tid;
+    if (j < ne) atomicAdd(&h[dg(ld.key(j), j)], 1u);
+  }
+  __syncthreads();
+  hist[(size_t)tid * n_tiles + blockIdx.x] = h[tid];
+}
+
+// ------------------------------------------------------------------ pass kernel 2: row scan
+// One CTA per digit: exclusive scan of its row of per-tile counts, in place; row total out.
+__global__ void __launch_bounds__(kThreads)
+k_rowscan(uint32_t* __restrict__ hist, int n_tiles, uint32_t* __restrict__ tot) {
+  __shared__ unsigned warp_sum[kWarps];
+  uint32_t* row = hist + (size_t)blockIdx.x * n_tiles;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int per = (n_tiles + kThreads - 1) / kThreads;
+  const int b = tid * per;
+  const int e = min(b + per, n_tiles);
+  unsigned s = 0;
+  for (int i = b; i < e; ++i) s += row[i];
+  unsigned inc = s;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    unsigned v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += v;
+  }
+  if (lane == 31) warp_sum[w] = inc;
+  __syncthreads();
+  unsigned wbase = 0, total = 0;
+#pragma unroll
+  for (int i = 0; i < kWarps; ++i) {
+    unsigned v = warp_sum[i];
+    if (i < w) wbase += v;
+    total += v;
+  }
+  unsigned run = wbase + inc - s;
+  for (int i = b; i < e; ++i) {
+    unsigned v = row[i];
+    row[i] = run;
+    run += v;
+  }
+  if (tid == 0) tot[blockIdx.x] = total;
+}
+
+// ------------------------------------------------------------------ pass kernel 3: scatter
+template <typename KeyT, typename Loader, typename DigitFn, typename KeyOutT>
+__global__ void __launch_bounds__(kThreads)
+k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
+          const uint32_t* __restrict__ hist, const uint32_t* __restrict__ tot,
+          KeyOutT* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+          int32_t* __restrict__ pos_out, int32_t* __restrict__ offsets_out, int n_bins) {
+  __shared__ unsigned cnt[kWarps][256];
+  __shared__ unsigned warp_sum[kWarps];
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int64_t ne = eff_n(n, n_dev);
+#pragma unroll
+  for (int i = 0; i < kWarps; ++i) cnt[i][tid] = 0;
+
+  // global digit base: exclusive scan over the 256 digit totals (thread d <-> digit d)
+  unsigned t = tot[tid];
+  unsigned inc = t;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    unsigned v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += v;
+  }
+  if (lane == 31) warp_sum[w] = inc;
+  __syncthreads();
+  unsigned wbase = 0;
+#pragma unroll
+  for (int i = 0; i < kWarps; ++i)
+    if (i < w) wbase += warp_sum[i];
+  const unsigned dbase = wbase + inc - t;  // first output slot of digit `tid`
+  if (offsets_out && blockIdx.x == 0) {     // partition: offsets[S+1]
+    if (tid < n_bins) offsets_out[tid] = (int32_t)dbase;
+    if (tid == n_bins) offsets_out[tid] = (int32_t)ne;
+  }
+
+  const int64_t wbeg = (int64_t)blockIdx.x * kTile + w * (32 * kItems);
+  KeyT key[kItems];
+  unsigned dig[kItems], rank[kItems];
+  const unsigned lt = edl_lanemask_lt();
+#pragma unroll
+  for (int k = 0; k < kItems; ++k) {
+    int64_t j = wbeg + k * 32 + lane;
+    bool valid = j < ne;
+    key[k] = valid ? ld.key(j) : (KeyT)0;
+    dig[k] = valid ? dg(key[k], j) : 256u;
+    unsigned mask = __match_any_sync(0xffffffffu, dig[k]);
+    int leader = __ffs(mask) - 1;
+    unsigned prev = 0;
+    if (lane == leader && valid) prev = cnt[w][dig[k]];
+    prev = __shfl_sync(0xffffffffu, prev, leader);
+    rank[k] = prev + __popc(mask & lt);
+    if (lane == leader && valid) cnt[w][dig[k]] = prev + __popc(mask);
+    __syncwarp();
+  }
+  __syncthreads();
+  {
+    unsigned run = dbase + hist[(size_t)tid * n_tiles + blockIdx.x];
+#pragma unroll
+    for (int i = 0; i < kWarps; ++i) {
+      unsigned c = cnt[i][tid];
+      cnt[i][tid] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < kItems; ++k) {
+    int64_t j = wbeg + k * 32 + lane;
+    if (j < ne) {
+      unsigned p = cnt[w][dig[k]] + rank[k];
+      uint32_t v = ld.val(j);
+      keys_out[p] = (KeyOutT)key[k];
+      vals_out[p] = v;
+      if (pos_out) pos_out[v] = (int32_t)p;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ unique kernels
+template <typename KeyT>
+__global__ void __launch_bounds__(kThreads)
+k_head_count(const KeyT* __restrict__ keys, int64_t n, const int32_t* n_dev, uint32_t* __restrict__ tile_heads) {
+  __shared__ unsigned warp_sum[kWarps];
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int64_t ne = eff_n(n, n_dev);
+  const int64_t base = (int64_t)blockIdx.x * kTile;
+  unsigned c = 0;
+#pragma unroll
+  for (int k = 0; k < kItems; ++k) {
+    int64_t i = base + k * kThreads + tid;
+    if (i < ne) c += (i == 0 || keys[i] != keys[i - 1]) ? 1u : 0u;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if (lane == 0) warp_sum[w] = c;
+  __syncthreads();
+  if (tid == 0) {
+    unsigned s = 0;
+#pragma unroll
+    for (int i = 0; i < kWarps; ++i) s += warp_sum[i];
+    tile_heads[blockIdx.x] = s;
+  }
+}
+
+// single CTA: exclusive scan over the tile head counts; publishes U and seg_offsets[U] = n
+__global__ void __launch_bounds__(1024)
+k_scan_tiles(uint32_t* __restrict__ tile_heads, int n_tiles, int64_t n, const int32_t* n_dev,
+             int32_t* __restrict__ n_unique, int32_t* __restrict__ seg_offsets) {
+  __shared__ unsigned warp_sum[32];
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int per = (n_tiles + 1023) / 1024;
+  const int b = tid * per, e = min(b + per, n_tiles);
+  unsigned s = 0;
+  for (int i = b; i < e; ++i) s += tile_heads[i];
+  unsigned inc = s;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    unsigned v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += v;
+  }
+  if (lane == 31) warp_sum[w] = inc;
+  __syncthreads();
+  unsigned wbase = 0, total = 0;
+  for (int i = 0; i < 32; ++i) {
+    unsigned v = warp_sum[i];
+    if (i < w) wbase += v;
+    total += v;
+  }
+  unsigned run = wbase + inc - s;
+  for (int i = b; i < e; ++i) {
+    unsigned v = tile_heads[i];
+    tile_heads[i] = run;
+    run += v;
+  }
+  if (tid == 0) {
+    *n_unique = (int32_t)total;
+    seg_offsets[total] = (int32_t)eff_n(n, n_dev);
+  }
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(kThreads)
+k_unique_write(const KeyT* __restrict__ keys, const uint32_t* __restrict__ order, int64_t n,
+               const int32_t* n_dev, const uint32_t* __restrict__ tile_base,
+               int64_t* __restrict__ uniq, int32_t* __restrict__ seg_offsets,
+               int32_t* __restrict__ inverse) {
+  __shared__ unsigned warp_sum[kWarps];
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int64_t ne = eff_n(n, n_dev);
+  const int64_t base = (int64_t)blockIdx.x * kTile + (int64_t)tid * kItems;  // blocked
+  KeyT key[kItems];
+  unsigned flag[kItems];
+  unsigned c = 0;
+  KeyT prev = 0;
+  if (base > 0 && base <= ne) prev = keys[base - 1];
+#pragma unroll
+  for (int k = 0; k < kItems; ++k) {
+    int64_t i = base + k;
+    bool valid = i < ne;
+    key[k] = valid ? keys[i] : (KeyT)0;
+    flag[k] = (valid && (i == 0 || key[k] != prev)) ? 1u : 0u;
+    prev = key[k];
+    c += flag[k];
+  }
+  unsigned inc = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    unsigned v = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += v;
+  }
+  if (lane == 31) warp_sum[w] = inc;
+  __syncthreads();
+  unsigned wbase = 0;
+#pragma unroll
+  for (int i = 0; i < kWarps; ++i)
+    if (i < w) wbase += warp_sum[i];
+  unsigned run = tile_base[blockIdx.x] + wbase + inc - c;  // heads strictly before my items
+#pragma unroll
+  for (int k = 0; k < kItems; ++k) {
+    int64_t i = base + k;
+    if (i < ne) {
+      run += flag[k];
+      unsigned u = run - 1;
+      if (flag[k]) {
+        uniq[u] = (int64_t)key[k];
+        seg_offsets[u] = (int32_t)i;
+      }
+      if (inverse) inverse[order[i]] = (int32_t)u;
+    }
+  }
+}
+
+__global__ void k_counts(const int32_t* __restrict__ seg_offsets, const int32_t* __restrict__ n_unique,
+                         int32_t* __restrict__ counts) {
+  const int U = *n_unique;
+  for (int u = blockIdx.x * blockDim.x + threadIdx.x; u < U; u += gridDim.x * blockDim.x)
+    counts[u] = seg_offsets[u + 1] - seg_offsets[u];
+}
+
+// A2: digit = (per-table id) mod S
+__global__ void __launch_bounds__(kThreads)
+k_shard_digits(const int64_t* __restrict__ keys, int64_t n, const int32_t* n_dev,
+               const int64_t* __restrict__ layout, unsigned S, uint8_t* __restrict__ dig) {
+  __shared__ EdlLayoutSmem L;
+  edl_layout_load(&L, layout);
+  __syncthreads();
+  const int64_t ne = eff_n(n, n_dev);
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < ne;
+       j += (int64_t)gridDim.x * blockDim.x) {
+    int t; unsigned long long id;
+    edl_split_key(&L, keys[j], &t, &id);
+    dig[j] = (uint8_t)(id % S);
+  }
+}
+
+__global__ void k_empty_unique(int32_t* n_unique, int32_t* seg_offsets) {
+  *n_unique = 0;
+  seg_offsets[0] = 0;
+}
+
+// ------------------------------------------------------------------ workspace carving
+struct UniqueWs {
+  void* keysA; void* keysB; uint32_t* valsB; uint32_t* hist; uint32_t* tot; uint32_t* tile_heads;
+  size_t bytes;
+};
+
+UniqueWs carve_unique(void* ws, int64_t n, int key_bits) {
+  const size_t kb = key_bits <= 32 ? 4 : 8;
+  const int64_t tiles = edl_cdiv(n > 0 ? n : 1, kTile);
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = edl_align_up(off + bytes, 256); return o; };
+  size_t oA = take((size_t)n * kb), oB = take((size_t)n * kb), oV = take((size_t)n * 4);
+  size_t oH = take((size_t)256 * tiles * 4), oT = take(256 * 4), oC = take((size_t)(tiles + 1) * 4);
+  UniqueWs r;
+  char* p = (char*)ws;
+  r.keysA = p + oA; r.keysB = p + oB; r.valsB = (uint32_t*)(p + oV);
+  r.hist = (uint32_t*)(p + oH); r.tot = (uint32_t*)(p + oT); r.tile_heads = (uint32_t*)(p + oC);
+  r.bytes = off;
+  return r;
+}
+
+template <typename KeyT>
+int unique_impl(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64_t* field_base,
+                int n_fields, int key_bits, int64_t* uniq, int32_t* inverse, int32_t* counts,
+                int32_t* order, int32_t* seg_offsets, int32_t* n_unique, const UniqueWs& W,
+                cudaStream_t st) {
+  const int tiles = (int)edl_cdiv(n, kTile);
+  const int passes = (key_bits + 7) / 8;
+  KeyT* kbuf[2] = {(KeyT*)W.keysA, (KeyT*)W.keysB};
+  uint32_t* vbuf[2];
+  // the last pass must land the payload in `order`
+  vbuf[(passes - 1) & 1] = (uint32_t*)order;
+  vbuf[(passes & 1)] = W.valsB;
+  for (int p = 0; p < passes; ++p) {
+    BitDigit<KeyT> dg{p * 8};
+    KeyT* ko = kbuf[p & 1];
+    uint32_t* vo = vbuf[p & 1];
+    if (p == 0) {
+      IdsLoader<KeyT> ld{ids, field_base, n_fields};
+      k_hist<KeyT><<<tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, tiles, W.hist);
+      k_rowscan<<<256, kThreads, 0, st>>>(W.hist, tiles, W.tot);
+      k_scatter<KeyT><<<tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, tiles, W.hist, W.tot, ko, vo,
+                                                  (int32_t*)nullptr, (int32_t*)nullptr, 0);
+    } else {
+      PairLoader<KeyT> ld{kbuf[(p - 1) & 1], vbuf[(p - 1) & 1]};
+      k_hist<KeyT><<<tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, tiles, W.hist);
+      k_rowscan<<<256, kThreads, 0, st>>>(W.hist, tiles, W.tot);
+      k_scatter<KeyT><<<tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, tiles, W.hist, W.tot, ko, vo,
+                                                  (int32_t*)nullptr, (int32_t*)nullptr, 0);
+    }
+  }
+  EDL_LAUNCH_CHECK("radix passes");
+  const KeyT* sorted = kbuf[(passes - 1) & 1];
+  k_head_count<KeyT><<<tiles, kThreads, 0, st>>>(sorted, n, n_dev, W.tile_heads);
+  k_scan_tiles<<<1, 1024, 0, st>>>(W.tile_heads, tiles, n, n_dev, n_unique, seg_offsets);
+  k_unique_write<KeyT><<<tiles, kThreads, 0, st>>>(sorted, (const uint32_t*)order, n, n_dev,
+                                                   W.tile_heads, uniq, seg_offsets, inverse);
+  if (counts) {
+    int g = (int)std::min<int64_t>(edl_cdiv(n, 256), EDL_SM_COUNT * 8);
+    k_counts<<<g, 256, 0, st>>>(seg_offsets, n_unique, counts);
+  }
+  EDL_LAUNCH_CHECK("unique kernels");
+  return EDL_OK;
+}
+
+}  // namespace
+
+extern "C" size_t edl_unique_workspace_bytes(int64_t n, int key_bits) {
+  if (n < 0) return 0;
+  return carve_unique(nullptr, n, key_bits).bytes;
+}
+
+extern "C" int edl_unique(const int64_t* ids, int64_t n, const int32_t* n_dev,
+                          const int64_t* field_base, int n_fields, int key_bits, int64_t* uniq,
+                          int32_t* inverse, int32_t* counts, int32_t* order, int32_t* seg_offsets,
+                          int32_t* n_unique, void* workspace, size_t workspace_bytes,
+                          edl_stream_t stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  EDL_REQUIRE(n >= 0 && n < (int64_t)0x7fff0000, EDL_EINVAL, "edl_unique: n=%lld out of range", (long long)n);
+  EDL_REQUIRE(key_bits >= 1 && key_bits <= 64, EDL_EINVAL, "edl_unique: key_bits=%d not in 1..64", key_bits);
+  EDL_REQUIRE(uniq && order && seg_offsets && n_unique, EDL_EINVAL,
+              "edl_unique: uniq, order, seg_offsets and n_unique are required");
+  EDL_REQUIRE(!field_base || n_fields > 0, EDL_EINVAL, "edl_unique: n_fields must be > 0 with field_base");
+  if (n == 0) {
+    k_empty_unique<<<1, 1, 0, st>>>(n_unique, seg_offsets);
+    EDL_LAUNCH_CHECK("k_empty_unique");
+    return EDL_OK;
+  }
+  EDL_REQUIRE(ids, EDL_EINVAL, "edl_unique: ids is null");
+  UniqueWs W = carve_unique(workspace, n, key_bits);
+  EDL_REQUIRE(workspace && workspace_bytes >= W.bytes, EDL_EWORKSPACE,
+              "edl_unique: workspace %zu < required %zu", workspace_bytes, W.bytes);
+  if (key_bits <= 32)
+    return unique_impl<uint32_t>(ids, n, n_dev, field_base, n_fields, key_bits, uniq, inverse, counts,
+                                 order, seg_offsets, n_unique, W, st);
+  return unique_impl<uint64_t>(ids, n, n_dev, field_base, n_fields, key_bits, uniq, inverse, counts,
+                               order, seg_offsets, n_unique, W, st);
+}
+
+// --------------------------------------------------------------------------------- A2
+namespace {
+struct PartWs { uint8_t* dig; uint32_t* hist; uint32_t* tot; size_t bytes; };
+PartWs carve_part(void* ws, int64_t n) {
+  const int64_t tiles = edl_cdiv(n > 0 ? n : 1, kTile);
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = edl_align_up(off + bytes, 256); return o; };
+  size_t oD = take((size_t)n), oH = take((size_t)256 * tiles * 4), oT = take(256 * 4);
+  PartWs r; char* p = (char*)ws;
+  r.dig = (uint8_t*)(p + oD); r.hist = (uint32_t*)(p + oH); r.tot = (uint32_t*)(p + oT); r.bytes = off;
+  return r;
+}
+__global__ void k_zero_offsets(int32_t* offsets, int nb) {
+  if (threadIdx.x <= nb) offsets[threadIdx.x] = 0;
+}
+}  // namespace
+
+extern "C" size_t edl_partition_mod_workspace_bytes(int64_t n, int num_shards) {
+  (void)num_shards;
+  if (n < 0) return 0;
+  return carve_part(nullptr, n).bytes;
+}
+
+extern "C" int edl_partition_mod(const int64_t* keys, int64_t n, const int32_t* n_dev,
+                                 const int64_t* layout, int num_shards, int64_t* keys_out,
+                                 int32_t* offsets, int32_t* perm, int32_t* pos, void* workspace,
+                                 size_t workspace_bytes, edl_stream_t stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  EDL_REQUIRE(n >= 0 && n < (int64_t)0x7fff0000, EDL_EINVAL, "edl_partition_mod: n=%lld out of range", (long long)n);
+  EDL_REQUIRE(num_shards >= 1 && num_shards <= 255, EDL_EINVAL,
+              "edl_partition_mod: num_shards=%d not in 1..255", num_shards);
+  EDL_REQUIRE(keys_out && offsets && perm, EDL_EINVAL, "edl_partition_mod: null output");
+  if (n == 0) {
+    k_zero_offsets<<<1, 256, 0, st>>>(offsets, num_shards);
+    EDL_LAUNCH_CHECK("k_zero_offsets");
+    return EDL_OK;
+  }
+  EDL_REQUIRE(keys, EDL_EINVAL, "edl_partition_mod: keys is null");
+  PartWs W = carve_part(workspace, n);
+  EDL_REQUIRE(workspace && workspace_bytes >= W.bytes, EDL_EWORKSPACE,
+              "edl_partition_mod: workspace %zu < required %zu", workspace_bytes, W.bytes);
+  const int tiles = (int)edl_cdiv(n, kTile);
+  int g = (int)std::min<int64_t>(edl_cdiv(n, kThreads), EDL_SM_COUNT * 8);
+  k_shard_digits<<<g, kThreads, 0, st>>>(keys, n, n_dev, layout, (unsigned)num_shards, W.dig);
+  KeyIndexLoader ld{keys};
+  ArrayDigit dg{W.dig};
+  k_hist<int64_t><<<tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, tiles, W.hist);
+  k_rowscan<<<256, kThreads, 0, st>>>(W.hist, tiles, W.tot);
+  k_scatter<int64_t><<<tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, tiles, W.hist, W.tot, keys_out,
+                                                 (uint32_t*)perm, pos, offsets, num_shards);
+  EDL_LAUNCH_CHECK("partition kernels");
+  return EDL_OK;
+}

@@ -1,0 +1,281 @@
+"""Thin torch-tensor wrappers over the C ABI (include/edlsparse.h).
+
+torch is plumbing here: it owns device memory and streams.  Every function enqueues on
+torch's current CUDA stream and returns without synchronising; counts produced on the device
+stay on the device (`n_unique` tensors) unless the caller asks for a trimmed result.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import OptParams, check
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    if t is None:
+        return None
+    return t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _need(t: torch.Tensor, dtype, name: str):
+    if not t.is_cuda:
+        raise _lib.EdlError(f"{name} must be a CUDA tensor (there is no CPU path)")
+    if t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+    return t
+
+
+def _ws(nbytes: int, device) -> torch.Tensor:
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
+def key_bits_for(total_rows: int) -> int:
+    """Number of significant bits of a fused key in [0, total_rows)."""
+    return max(1, int(total_rows - 1).bit_length())
+
+
+# ------------------------------------------------------------------------------- init / fill
+def init_rows(slab: torch.Tensor, layout: torch.Tensor, seed: int, row_begin: int = 0,
+              n_rows: Optional[int] = None):
+    lib = _lib.load()
+    _need(slab, torch.float32, "slab")
+    n_rows = slab.shape[0] - row_begin if n_rows is None else n_rows
+    check(lib.edl_init_rows(_ptr(slab), slab.shape[1], _ptr(layout), row_begin, n_rows,
+                            C.c_uint64(seed & (2 ** 64 - 1)), _stream()), "edl_init_rows")
+
+
+def fill(t: torch.Tensor, value: float):
+    lib = _lib.load()
+    _need(t, torch.float32, "t")
+    check(lib.edl_fill_f32(_ptr(t), t.numel(), C.c_float(value), _stream()), "edl_fill_f32")
+
+
+# ------------------------------------------------------------------------------- A1
+@dataclass
+class UniqueResult:
+    """Device-resident result of A1.  Arrays have capacity n; the first U entries are valid."""
+    uniq: torch.Tensor          # int64 [n]
+    inverse: Optional[torch.Tensor]  # int32 [n]
+    counts: Optional[torch.Tensor]   # int32 [n]
+    order: torch.Tensor         # int32 [n]
+    seg_offsets: torch.Tensor   # int32 [n+1]
+    n_unique: torch.Tensor      # int32 [1] on device
+    n: int
+
+    def count(self) -> int:
+        """Host value of U (synchronises)."""
+        return int(self.n_unique.item())
+
+    def trimmed(self):
+        u = self.count()
+        return (self.uniq[:u], self.inverse, None if self.counts is None else self.counts[:u],
+                self.order, self.seg_offsets[:u + 1])
+
+
+def unique(ids: torch.Tensor, field_base: Optional[torch.Tensor] = None, key_bits: int = 64, *,
+           want_inverse: bool = True, want_counts: bool = True,
+           n_dev: Optional[torch.Tensor] = None, out: Optional[UniqueResult] = None,
+           workspace: Optional[torch.Tensor] = None) -> UniqueResult:
+    lib = _lib.load()
+    _need(ids, torch.int64, "ids")
+    n = ids.numel()
+    dev = ids.device
+    n_fields = 0
+    if field_base is not None:
+        _need(field_base, torch.int64, "field_base")
+        n_fields = field_base.numel()
+    if out is None:
+        out = UniqueResult(
+            uniq=torch.empty(n, dtype=torch.int64, device=dev),
+            inverse=torch.empty(n, dtype=torch.int32, device=dev) if want_inverse else None,
+            counts=torch.empty(n, dtype=torch.int32, device=dev) if want_counts else None,
+            order=torch.empty(n, dtype=torch.int32, device=dev),
+            seg_offsets=torch.empty(n + 1, dtype=torch.int32, device=dev),
+            n_unique=torch.empty(1, dtype=torch.int32, device=dev), n=n)
+    need = lib.edl_unique_workspace_bytes(n, key_bits)
+    if workspace is None or workspace.numel() < need:
+        workspace = _ws(need, dev)
+    check(lib.edl_unique(_ptr(ids), n, _ptr(n_dev), _ptr(field_base), n_fields, key_bits,
+                         _ptr(out.uniq), _ptr(out.inverse), _ptr(out.counts), _ptr(out.order),
+                         _ptr(out.seg_offsets), _ptr(out.n_unique), _ptr(workspace),
+                         workspace.numel(), _stream()), "edl_unique")
+    return out
+
+
+# ------------------------------------------------------------------------------- A2
+@dataclass
+class PartitionResult:
+    keys: torch.Tensor      # int64 [n] grouped by shard
+    offsets: torch.Tensor   # int32 [S+1]
+    perm: torch.Tensor      # int32 [n] original position of each output
+    pos: Optional[torch.Tensor]  # int32 [n] output position of each input
+
+
+def partition_mod(keys: torch.Tensor, layout: Optional[torch.Tensor], num_shards: int, *,
+                  n_dev: Optional[torch.Tensor] = None, want_pos: bool = True,
+                  workspace: Optional[torch.Tensor] = None) -> PartitionResult:
+    lib = _lib.load()
+    _need(keys, torch.int64, "keys")
+    n = keys.numel()
+    dev = keys.device
+    res = PartitionResult(torch.empty(n, dtype=torch.int64, device=dev),
+                          torch.empty(num_shards + 1, dtype=torch.int32, device=dev),
+                          torch.empty(n, dtype=torch.int32, device=dev),
+                          torch.empty(n, dtype=torch.int32, device=dev) if want_pos else None)
+    need = lib.edl_partition_mod_workspace_bytes(n, num_shards)
+    if workspace is None or workspace.numel() < need:
+        workspace = _ws(need, dev)
+    check(lib.edl_partition_mod(_ptr(keys), n, _ptr(n_dev), _ptr(layout), num_shards,
+                                _ptr(res.keys), _ptr(res.offsets), _ptr(res.perm), _ptr(res.pos),
+                                _ptr(workspace), workspace.numel(), _stream()), "edl_partition_mod")
+    return res
+
+
+# ------------------------------------------------------------------------------- A3
+def gather_keys(slab: torch.Tensor, keys: torch.Tensor, layout: Optional[torch.Tensor] = None, *,
+                n_dev: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None):
+    lib = _lib.load()
+    _need(slab, torch.float32, "slab")
+    _need(keys, torch.int64, "keys")
+    n, dim = keys.numel(), slab.shape[1]
+    if out is None:
+        out = torch.empty((n, dim), dtype=torch.float32, device=slab.device)
+    check(lib.edl_gather_keys(_ptr(slab), dim, _ptr(keys), n, _ptr(n_dev), _ptr(layout), _ptr(out),
+                              _stream()), "edl_gather_keys")
+    return out
+
+
+def gather_ids(slab: torch.Tensor, ids: torch.Tensor, field_base: Optional[torch.Tensor], *,
+               out: Optional[torch.Tensor] = None):
+    lib = _lib.load()
+    _need(slab, torch.float32, "slab")
+    _need(ids, torch.int64, "ids")
+    n, dim = ids.numel(), slab.shape[1]
+    if out is None:
+        out = torch.empty((n, dim), dtype=torch.float32, device=slab.device)
+    nf = 0 if field_base is None else field_base.numel()
+    check(lib.edl_gather_ids(_ptr(slab), dim, _ptr(ids), n, _ptr(field_base), nf, _ptr(out),
+                             _stream()), "edl_gather_ids")
+    return out
+
+
+def expand(rows: torch.Tensor, index: torch.Tensor, *, out: Optional[torch.Tensor] = None):
+    lib = _lib.load()
+    _need(rows, torch.float32, "rows")
+    _need(index, torch.int32, "index")
+    n, dim = index.numel(), rows.shape[1]
+    if out is None:
+        out = torch.empty((n, dim), dtype=torch.float32, device=rows.device)
+    check(lib.edl_expand(_ptr(rows), dim, _ptr(index), n, _ptr(out), _stream()), "edl_expand")
+    return out
+
+
+def compose_index(index: torch.Tensor, mapping: torch.Tensor):
+    lib = _lib.load()
+    _need(index, torch.int32, "index")
+    _need(mapping, torch.int32, "mapping")
+    out = torch.empty_like(index)
+    check(lib.edl_compose_index(_ptr(index), _ptr(mapping), index.numel(), _ptr(out), _stream()),
+          "edl_compose_index")
+    return out
+
+
+def scatter_rows(rows: torch.Tensor, pos: torch.Tensor, out: torch.Tensor, *,
+                 n_dev: Optional[torch.Tensor] = None):
+    lib = _lib.load()
+    _need(rows, torch.float32, "rows")
+    _need(pos, torch.int32, "pos")
+    _need(out, torch.float32, "out")
+    check(lib.edl_scatter_rows(_ptr(rows), rows.shape[1], _ptr(pos), pos.numel(), _ptr(n_dev),
+                               _ptr(out), _stream()), "edl_scatter_rows")
+    return out
+
+
+# ------------------------------------------------------------------------------- A4 / A5
+def segreduce(grad: torch.Tensor, order: torch.Tensor, seg_offsets: torch.Tensor,
+              n_unique: torch.Tensor, max_unique: int, *, out_pos: Optional[torch.Tensor] = None,
+              out: Optional[torch.Tensor] = None, workspace: Optional[torch.Tensor] = None):
+    lib = _lib.load()
+    _need(grad, torch.float32, "grad")
+    _need(order, torch.int32, "order")
+    _need(seg_offsets, torch.int32, "seg_offsets")
+    dim = grad.shape[1]
+    if out is None:
+        out = torch.empty((max_unique, dim), dtype=torch.float32, device=grad.device)
+    need = lib.edl_segreduce_workspace_bytes(max_unique, dim)
+    if workspace is None or workspace.numel() < need:
+        workspace = _ws(need, grad.device)
+    check(lib.edl_segreduce(_ptr(grad), dim, _ptr(order), _ptr(seg_offsets), _ptr(n_unique),
+                            max_unique, _ptr(out_pos), _ptr(out), _ptr(workspace),
+                            workspace.numel(), _stream()), "edl_segreduce")
+    return out
+
+
+def segreduce_update(slab: torch.Tensor, slot0: torch.Tensor, slot1: Optional[torch.Tensor],
+                     uniq: torch.Tensor, order: torch.Tensor, seg_offsets: torch.Tensor,
+                     n_unique: torch.Tensor, max_unique: int, grad: torch.Tensor,
+                     layout: Optional[torch.Tensor], opt: OptParams,
+                     touched: Optional[torch.Tensor] = None,
+                     workspace: Optional[torch.Tensor] = None):
+    lib = _lib.load()
+    _need(slab, torch.float32, "slab")
+    _need(slot0, torch.float32, "slot0")
+    _need(grad, torch.float32, "grad")
+    _need(uniq, torch.int64, "uniq")
+    dim = slab.shape[1]
+    if grad.shape[1] != dim:
+        raise ValueError("grad and slab dims differ")
+    need = lib.edl_segreduce_workspace_bytes(max_unique, dim)
+    if workspace is None or workspace.numel() < need:
+        workspace = _ws(need, slab.device)
+    check(lib.edl_segreduce_update(_ptr(slab), _ptr(slot0), _ptr(slot1), dim, _ptr(uniq),
+                                   _ptr(order), _ptr(seg_offsets), _ptr(n_unique), max_unique,
+                                   _ptr(grad), _ptr(layout), C.byref(opt), _ptr(touched),
+                                   _ptr(workspace), workspace.numel(), _stream()),
+          "edl_segreduce_update")
+
+
+# ------------------------------------------------------------------------------- A6
+def export_count(touched: torch.Tensor, n_rows: int) -> torch.Tensor:
+    lib = _lib.load()
+    n_out = torch.empty(1, dtype=torch.int32, device=touched.device)
+    ws = _ws(lib.edl_export_workspace_bytes(n_rows), touched.device)
+    check(lib.edl_export_count(_ptr(touched), n_rows, _ptr(n_out), _ptr(ws), ws.numel(), _stream()),
+          "edl_export_count")
+    return n_out
+
+
+def export_shard(slab, slot0, slot1, touched, n_rows: int, layout, capacity: int):
+    """-> keys[capacity] i64, rows, slot0, slot1 [capacity, dim], n_out (device int32)."""
+    lib = _lib.load()
+    dev, dim = slab.device, slab.shape[1]
+    keys = torch.empty(capacity, dtype=torch.int64, device=dev)
+    rows = torch.empty((capacity, dim), dtype=torch.float32, device=dev)
+    o0 = torch.empty_like(rows) if slot0 is not None else None
+    o1 = torch.empty_like(rows) if slot1 is not None else None
+    n_out = torch.empty(1, dtype=torch.int32, device=dev)
+    ws = _ws(lib.edl_export_workspace_bytes(n_rows), dev)
+    check(lib.edl_export_shard(_ptr(slab), _ptr(slot0), _ptr(slot1), dim, _ptr(touched), n_rows,
+                               _ptr(layout), capacity, _ptr(keys), _ptr(rows), _ptr(o0), _ptr(o1),
+                               _ptr(n_out), _ptr(ws), ws.numel(), _stream()), "edl_export_shard")
+    return keys, rows, o0, o1, n_out
+
+
+def import_shard(slab, slot0, slot1, touched, layout, keys, rows, slot0_in, slot1_in):
+    lib = _lib.load()
+    _need(keys, torch.int64, "keys")
+    _need(rows, torch.float32, "rows")
+    check(lib.edl_import_shard(_ptr(slab), _ptr(slot0), _ptr(slot1), slab.shape[1], _ptr(touched),
+                               _ptr(layout), _ptr(keys), _ptr(rows), _ptr(slot0_in), _ptr(slot1_in),
+                               keys.numel(), _stream()), "edl_import_shard")

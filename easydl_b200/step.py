@@ -1,0 +1,63 @@
+"""The fused sparse step of one worker + PS shard pair on one GPU (S == 1 path).
+
+lookup : emb[j] = table[ids[j]]                              (A3, direct gather, no dedup)
+update : dedup(ids) -> segmented reduce of grad -> optimizer (A1 + A4 + A5)
+
+All buffers are allocated once; a step enqueues kernels on the current stream and never
+synchronises with the host.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+from . import kernels as K
+from .parameters import ShardParameters
+
+
+class SparseStep:
+    def __init__(self, params: ShardParameters, batch_size: int, n_fields: Optional[int] = None):
+        if params.num_shards != 1:
+            raise ValueError("SparseStep is the single-shard path; use ShardedSparseStep for S > 1")
+        self.params = params
+        self.F = params.layout.n_tables if n_fields is None else n_fields
+        self.B = int(batch_size)
+        self.N = self.B * self.F
+        dev = params.device
+        lib = _lib.load()
+        self.field_base = torch.from_numpy(params.layout.key_base[:self.F].copy()).to(dev)
+        self.key_bits = params.layout.key_bits
+        N, D = self.N, params.dim
+        self.emb = torch.empty((N, D), dtype=torch.float32, device=dev)
+        self.uq = K.UniqueResult(
+            uniq=torch.empty(N, dtype=torch.int64, device=dev), inverse=None, counts=None,
+            order=torch.empty(N, dtype=torch.int32, device=dev),
+            seg_offsets=torch.empty(N + 1, dtype=torch.int32, device=dev),
+            n_unique=torch.zeros(1, dtype=torch.int32, device=dev), n=N)
+        self.ws_unique = torch.empty(lib.edl_unique_workspace_bytes(N, self.key_bits),
+                                     dtype=torch.uint8, device=dev)
+        self.ws_seg = torch.empty(lib.edl_segreduce_workspace_bytes(N, D), dtype=torch.uint8, device=dev)
+        # launches per step (for bench.py's gpu_launches): gather 1; unique 3/pass + 3; update 2 + memset
+        self.launches_lookup = 1
+        self.launches_update = 3 * ((self.key_bits + 7) // 8) + 3 + 2
+
+    def lookup(self, ids: torch.Tensor) -> torch.Tensor:
+        """ids int64 [B, F] on the device -> emb [B*F, dim]."""
+        return K.gather_ids(self.params.slab, ids.view(-1), self.field_base, out=self.emb)
+
+    def dedup(self, ids: torch.Tensor) -> K.UniqueResult:
+        return K.unique(ids.view(-1), self.field_base, self.key_bits, want_inverse=False,
+                        want_counts=False, out=self.uq, workspace=self.ws_unique)
+
+    def update(self, ids: torch.Tensor, grad: torch.Tensor, uq: Optional[K.UniqueResult] = None):
+        """grad f32 [B*F, dim]: upstream gradient of emb."""
+        if uq is None:
+            uq = self.dedup(ids)
+        self.params.apply_gradients(uq, grad, self.N, self.ws_seg)
+
+    def run(self, ids: torch.Tensor, grad: torch.Tensor) -> torch.Tensor:
+        emb = self.lookup(ids)
+        self.update(ids, grad)
+        return emb

@@ -1,0 +1,167 @@
+/* edlsparse.h -- C ABI of libedlsparse.so: the B200 (sm_100a) sparse-embedding step of an
+ * EasyDL ElasticTrainer parameter-server job.
+ *
+ * Reference interface replaced: NONE EXISTS.  The snapshot holds no PS / worker code, no
+ * FFI and no operator interface.  The roles this library serves are
+ * named at ref:README.md:11 (ElasticTrainer), ref:README.md:27 (recover failed parameter
+ * servers and workers), ref:README.md:33-35 (scale PS / workers during training) and
+ * ref:docs/design/elastic-training-operator.md:39-44,65-85 (parameter_server / worker
+ * roles, replicas).  Each entry point below names the SURVEY.md section 8 row (A1..A7) and
+ * the lineage function it stands in for; the semantics are written down in SPEC.md.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - the caller owns every buffer, including scratch ("workspace"): ask the matching
+ *     *_workspace_bytes() function for the size.  The library allocates nothing;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*);
+ *   - return value: 0 (EDL_OK) or a negative EDL_E* code; edl_last_error_string() gives
+ *     the thread-local message.  Nothing throws, nothing aborts;
+ *   - "n_dev": where a count is produced on the device (the number of unique ids) the
+ *     consumers take the device pointer plus a host upper bound, so a whole step can be
+ *     enqueued without a host synchronisation;
+ *   - rows are fp32, row-major, `dim` a multiple of 4 (16-byte rows at least), row
+ *     pointers 16-byte aligned.
+ *
+ * Fused keys.  Table t has rows_t hash buckets; key(t, id) = key_base[t] + id with
+ * key_base the exclusive prefix sum of rows_t.  A `layout` is a device int64 array
+ *   [ T, S, shard, 0, key_base[0..T], local_base[0..T] ]      (4 + 2*(T+1) entries)
+ * where shard s of table t stores local row (id div S) at slab row local_base[t] + id div S
+ * and owns ids with id mod S == s (SPEC "Shard function").  layout == NULL means S == 1 and
+ * slab row == key.
+ */
+#ifndef EDLSPARSE_H_
+#define EDLSPARSE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EDL_OK 0
+#define EDL_EINVAL (-1)     /* bad argument (null pointer, dim not multiple of 4, ...) */
+#define EDL_ECUDA (-2)      /* a CUDA runtime call or launch failed */
+#define EDL_EWORKSPACE (-3) /* workspace too small */
+#define EDL_ELIMIT (-4)     /* size beyond a documented limit */
+
+#define EDL_OPT_ADAGRAD 0
+#define EDL_OPT_ADAM 1
+
+typedef void* edl_stream_t; /* cudaStream_t */
+
+int edl_version(void);
+const char* edl_last_error_string(void);
+
+/* ---- row initialisation (SPEC "Row initialisation"; lineage EmbeddingTable lazy init) ---
+ * Fills slab rows [row_begin, row_begin + n_rows) of this shard's slab with the pure
+ * function init(seed, t, id, c).  layout may be NULL (S == 1: slab row == fused key, tables
+ * located through key_base passed as `layout`-less call is not possible, so layout is
+ * required here). */
+int edl_init_rows(float* slab, int dim, const int64_t* layout, int64_t row_begin, int64_t n_rows,
+                  uint64_t seed, edl_stream_t stream);
+/* value fill for optimizer slots (Adagrad init_accum, Adam zeros) */
+int edl_fill_f32(float* dst, int64_t n, float value, edl_stream_t stream);
+
+/* ---- A1 dedup / unique (lineage deduplicate_indexed_slices, unique half) ---------------
+ * keys[j] = ids[j] + field_base[j % n_fields] (field_base NULL: keys = ids).
+ * Outputs (each nullable except uniq, order, seg_offsets, n_unique):
+ *   uniq[U] ascending int64, inverse[n] int32, counts[U] int32,
+ *   order[n] int32 = stable argsort(keys), seg_offsets[U+1] int32 (seg_offsets[U] = n),
+ *   n_unique: device int32 scalar U.
+ * Only the low key_bits bits of the keys may be non-zero (1..64).
+ * n_dev (nullable): device int32 holding the actual n (<= n); used when the input length
+ * itself was produced on the device. */
+size_t edl_unique_workspace_bytes(int64_t n, int key_bits);
+int edl_unique(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64_t* field_base,
+               int n_fields, int key_bits, int64_t* uniq, int32_t* inverse, int32_t* counts,
+               int32_t* order, int32_t* seg_offsets, int32_t* n_unique, void* workspace,
+               size_t workspace_bytes, edl_stream_t stream);
+
+/* ---- A2 hash-mod partition (lineage int_to_id / scatter_embedding_vector) --------------
+ * Stable partition of keys[0..n) by (per-table id mod S'), S' = num_shards (1..256), tables
+ * located through `layout` (only T and key_base are read; NULL = single table, id == key).
+ * Outputs: keys_out[n] grouped by shard, offsets[S'+1] int32, perm[n] int32 (original
+ * position of each output), pos[n] int32 (nullable; inverse of perm). */
+size_t edl_partition_mod_workspace_bytes(int64_t n, int num_shards);
+int edl_partition_mod(const int64_t* keys, int64_t n, const int32_t* n_dev, const int64_t* layout,
+                      int num_shards, int64_t* keys_out, int32_t* offsets, int32_t* perm,
+                      int32_t* pos, void* workspace, size_t workspace_bytes, edl_stream_t stream);
+
+/* ---- A3 embedding gather (lineage pull_embedding_vectors / EmbeddingTable.get) ---------
+ * edl_gather_keys : out[i] = slab[row(keys[i])], row() through `layout` (NULL: row = key).
+ * edl_gather_ids  : out[j] = slab[ids[j] + field_base[j % n_fields]]   (S == 1 direct lookup
+ *                   of a [B, F] id batch without a dedup).
+ * edl_expand      : out[j] = rows[index[j]], int32 index (worker-side expand by `inverse`).
+ * n_dev nullable as above. */
+int edl_gather_keys(const float* slab, int dim, const int64_t* keys, int64_t n, const int32_t* n_dev,
+                    const int64_t* layout, float* out, edl_stream_t stream);
+int edl_gather_ids(const float* slab, int dim, const int64_t* ids, int64_t n,
+                   const int64_t* field_base, int n_fields, float* out, edl_stream_t stream);
+int edl_expand(const float* rows, int dim, const int32_t* index, int64_t n, float* out,
+               edl_stream_t stream);
+/* index2 composition for the sharded path: out[j] = map[index[j]] (int32) */
+int edl_compose_index(const int32_t* index, const int32_t* map, int64_t n, int32_t* out,
+                      edl_stream_t stream);
+
+/* ---- A4 segmented gradient reduce (lineage deduplicate_indexed_slices, sum half) -------
+ * g_out[dst(u)] = sum over i in [seg_offsets[u], seg_offsets[u+1]) of grad[order[i]],
+ * accumulated in float64, rounded once to fp32.  dst(u) = out_pos ? out_pos[u] : u.
+ * n_unique_dev: device int32 U; max_unique: host upper bound. */
+size_t edl_segreduce_workspace_bytes(int64_t max_unique, int dim);
+int edl_segreduce(const float* grad, int dim, const int32_t* order, const int32_t* seg_offsets,
+                  const int32_t* n_unique_dev, int64_t max_unique, const int32_t* out_pos,
+                  float* g_out, void* workspace, size_t workspace_bytes, edl_stream_t stream);
+
+/* ---- A4 + A5 fused: reduce, then optimizer row update in place (lineage PS
+ * push_gradients -> optimizer kernel) -------------------------------------------------------
+ * For each unique u: g = segment sum as above; row = row(uniq[u]) through layout;
+ * Adagrad: acc += g*g; p -= lr*g/(sqrt(acc)+eps)                       (slot0 = acc)
+ * Adam   : m = b1*m+(1-b1)*g; v = b2*v+((1-b2)*g)*g; p -= lr_t*m/(sqrt(v)+eps)
+ *          (slot0 = m, slot1 = v; lr_t computed by the caller in float64)
+ * every operation rounded to fp32 separately (no FMA contraction).
+ * touched (nullable): bitmap, one bit per slab row, set for every updated row (A6 export). */
+typedef struct edl_opt_params {
+  int kind;     /* EDL_OPT_ADAGRAD / EDL_OPT_ADAM */
+  float lr;     /* Adagrad lr, or Adam lr_t */
+  float eps;
+  float beta1;  /* Adam only */
+  float beta2;  /* Adam only */
+} edl_opt_params;
+
+int edl_segreduce_update(float* slab, float* slot0, float* slot1, int dim, const int64_t* uniq,
+                         const int32_t* order, const int32_t* seg_offsets,
+                         const int32_t* n_unique_dev, int64_t max_unique, const float* grad,
+                         const int64_t* layout, const edl_opt_params* opt_host, uint32_t* touched,
+                         void* workspace, size_t workspace_bytes, edl_stream_t stream);
+
+/* ---- A6 elastic re-shard (lineage CheckpointSaver / restore_params_from_checkpoint) ----
+ * edl_export_count : n_out (device int32) = number of set bits in touched[0..n_rows).
+ * edl_export_shard : compacts the touched rows in ascending slab-row order into
+ *                    keys_out[n] (fused keys), rows_out / slot0_out / slot1_out [n, dim].
+ *                    capacity = size of the output buffers in rows.
+ * edl_import_shard : for each record i with (id mod S == shard) under `layout`: writes
+ *                    rows/slots into the slab and sets its touched bit; others are skipped
+ *                    (restore reads ALL old shard files and keeps its own ids). */
+size_t edl_export_workspace_bytes(int64_t n_rows);
+int edl_export_count(const uint32_t* touched, int64_t n_rows, int32_t* n_out, void* workspace,
+                     size_t workspace_bytes, edl_stream_t stream);
+int edl_export_shard(const float* slab, const float* slot0, const float* slot1, int dim,
+                     const uint32_t* touched, int64_t n_rows, const int64_t* layout,
+                     int64_t capacity, int64_t* keys_out, float* rows_out, float* slot0_out,
+                     float* slot1_out, int32_t* n_out, void* workspace, size_t workspace_bytes,
+                     edl_stream_t stream);
+int edl_import_shard(float* slab, float* slot0, float* slot1, int dim, uint32_t* touched,
+                     const int64_t* layout, const int64_t* keys, const float* rows,
+                     const float* slot0_in, const float* slot1_in, int64_t n,
+                     edl_stream_t stream);
+
+/* ---- A7 exchange helpers: permute rows for the all-to-all-v send buffers --------------
+ * out[i] = rows[perm[i]] is edl_expand.  Scatter form: out[pos[i]] = rows[i]. */
+int edl_scatter_rows(const float* rows, int dim, const int32_t* pos, int64_t n,
+                     const int32_t* n_dev, float* out, edl_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EDLSPARSE_H_ */
