@@ -422,14 +422,14 @@ extern "C" int edl_unique(const int64_t* ids, int64_t n, const int32_t* n_dev,
   cudaStream_t st = (cudaStream_t)stream;
   EDL_REQUIRE(n >= 0 && n < (int64_t)0x7fff0000, EDL_EINVAL, "edl_unique: n=%lld out of range", (long long)n);
   EDL_REQUIRE(key_bits >= 1 && key_bits <= 64, EDL_EINVAL, "edl_unique: key_bits=%d not in 1..64", key_bits);
-  EDL_REQUIRE(uniq && order && seg_offsets && n_unique, EDL_EINVAL,
-              "edl_unique: uniq, order, seg_offsets and n_unique are required");
+  EDL_REQUIRE(seg_offsets && n_unique, EDL_EINVAL, "edl_unique: seg_offsets and n_unique are required");
   EDL_REQUIRE(!field_base || n_fields > 0, EDL_EINVAL, "edl_unique: n_fields must be > 0 with field_base");
   if (n == 0) {
     k_empty_unique<<<1, 1, 0, st>>>(n_unique, seg_offsets);
     EDL_LAUNCH_CHECK("k_empty_unique");
     return EDL_OK;
   }
+  EDL_REQUIRE(uniq && order, EDL_EINVAL, "edl_unique: uniq and order are required");
   EDL_REQUIRE(ids, EDL_EINVAL, "edl_unique: ids is null");
   UniqueWs W = carve_unique(workspace, n, key_bits);
   EDL_REQUIRE(workspace && workspace_bytes >= W.bytes, EDL_EWORKSPACE,
@@ -472,13 +472,13 @@ extern "C" int edl_partition_mod(const int64_t* keys, int64_t n, const int32_t* 
   EDL_REQUIRE(n >= 0 && n < (int64_t)0x7fff0000, EDL_EINVAL, "edl_partition_mod: n=%lld out of range", (long long)n);
   EDL_REQUIRE(num_shards >= 1 && num_shards <= 255, EDL_EINVAL,
               "edl_partition_mod: num_shards=%d not in 1..255", num_shards);
-  EDL_REQUIRE(keys_out && offsets && perm, EDL_EINVAL, "edl_partition_mod: null output");
+  EDL_REQUIRE(offsets, EDL_EINVAL, "edl_partition_mod: offsets is null");
   if (n == 0) {
     k_zero_offsets<<<1, 256, 0, st>>>(offsets, num_shards);
     EDL_LAUNCH_CHECK("k_zero_offsets");
     return EDL_OK;
   }
-  EDL_REQUIRE(keys, EDL_EINVAL, "edl_partition_mod: keys is null");
+  EDL_REQUIRE(keys && keys_out && perm, EDL_EINVAL, "edl_partition_mod: null keys / keys_out / perm");
   PartWs W = carve_part(workspace, n);
   EDL_REQUIRE(workspace && workspace_bytes >= W.bytes, EDL_EWORKSPACE,
               "edl_partition_mod: workspace %zu < required %zu", workspace_bytes, W.bytes);
