@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""bench.py -- Criteo-shape sparse step samples/s on B200 (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N ...            # the CPU parameter-server path
+
+A "step" is one pass of the hot path over one synthetic Criteo-shape batch:
+lookup (A3) -> [upstream gradient, synthetic, resident] -> dedup (A1) -> segmented reduce +
+Adagrad row update (A4 + A5).  Default workload = BASELINE.json configs[1]: DeepFM-shape,
+26 tables x 10M rows x dim 64, batch 64K, Adagrad, one B200.  For N > 1 the tables are
+row-sharded over the N GPUs (id mod N) and every GPU brings its own 64K batch (weak scaling),
+exchanging ids / rows / gradients by NCCL all-to-all-v.
+
+One JSON line on stdout (rank 0).  `value` is device-resident throughput; `e2e` is the same
+step through the host-buffer PS API (ids H2D, embeddings D2H, gradients H2D each step).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "criteo_sparse_step_samples_per_s"
+UNIT = "samples/s"
+N_FIELDS = 26
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--rows", type=int, default=10_000_000, help="rows per table (global)")
+    ap.add_argument("--dim", type=int, default=64)
+    ap.add_argument("--batch", type=int, default=65536, help="samples per GPU per step")
+    ap.add_argument("--alpha", type=float, default=1.05)
+    ap.add_argument("--optimizer", default="adagrad", choices=["adagrad", "adam"])
+    ap.add_argument("--n-batches", type=int, default=8, help="distinct id batches cycled through")
+    ap.add_argument("--e2e-steps", type=int, default=10)
+    ap.add_argument("--cpu-steps", type=int, default=3, help="timed oracle steps for cpu_baseline")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return (f"deepfm-shape {N_FIELDS} tables x {a.rows} rows x dim {a.dim}, batch {a.batch}/GPU, "
+            f"{a.optimizer}, zipf {a.alpha}")
+
+
+def algorithmic_bytes(N, U, D, optimizer):
+    """compulsory HBM traffic of one step (ids 8 B, inverse 4 B, fp32)."""
+    lookup = 8 * N + 4 * D * U + 4 * D * N
+    if optimizer == "adagrad":
+        update = 4 * D * N + 4 * N + 16 * D * U
+    else:
+        update = 4 * D * N + 4 * N + 24 * D * U
+    return lookup, update
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+# ------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """Samples SM clock and throttle reasons through NVML while `active` is set."""
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.active, self._stop = [], set(), False, False
+        self.max_mhz = None
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # pragma: no cover
+            self.err = repr(e)
+        self.t = threading.Thread(target=self._run, daemon=True)
+        if self.ok:
+            self.t.start()
+
+    def _run(self):
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop:
+            if self.active:
+                try:
+                    self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                    try:
+                        r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                    except Exception:
+                        r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                    for bit, nm in names.items():
+                        if r & bit:
+                            self.reasons.add(nm)
+                except Exception:
+                    pass
+            time.sleep(0.01)
+
+    def result(self):
+        self._stop = True
+        if not self.ok or not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------ CPU arm
+def cpu_reference(a, threads: int, steps: int, warmup: int):
+    """The CPU parameter-server path (oracle port) on the host cores.  Tables are lazily
+    materialised; one untimed pass per distinct batch creates the rows so the timed steps
+    measure lookup + reduce + update, not row initialisation."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    from oracle import edl_oracle as O
+    rows = [a.rows] * N_FIELDS
+    opt = O.OptimizerSpec.adagrad() if a.optimizer == "adagrad" else O.OptimizerSpec.adam()
+    shard = O.OracleShard(rows, a.dim, opt)
+    nb = max(1, min(a.n_batches, 2))
+    batches = [O.criteo_batch(rows, a.batch, a.alpha, step=i)[1] for i in range(nb)]
+    grad = O.synthetic_grad(a.batch * N_FIELDS, a.dim)
+    for ids in batches:  # materialise
+        shard.materialise(np.unique(O.fuse_keys(ids, shard.bases)))
+    pool = ThreadPoolExecutor(threads) if threads > 1 else None
+    for i in range(warmup):
+        O.sparse_step_per_table(shard, batches[i % nb], grad, pool)
+    t0 = time.perf_counter()
+    for i in range(steps):
+        O.sparse_step_per_table(shard, batches[i % nb], grad, pool)
+    dt = time.perf_counter() - t0
+    return a.batch * steps / dt, dt / steps
+
+
+def run_reference_arm(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    threads = min(cores, N_FIELDS)
+    steps = max(1, min(a.steps, 5))
+    warm = max(1, min(a.warmup, 1))
+    v, spp = cpu_reference(a, threads, steps, warm)
+    sample = (f"{steps} full steps (batch {a.batch}, {N_FIELDS} tables, dim {a.dim}) of the NumPy oracle, "
+              f"one table per thread on {threads} threads, rows pre-materialised")
+    line = {
+        "metric": METRIC, "value": v, "unit": UNIT, "impl": "reference", "n_gpus": a.gpus,
+        "steps": steps, "warmup": warm, "ms_per_step": spp * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(a), "note": "CPU PS path; one host, all cores; the N GPUs are unused"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------ GPU arm
+def run_b200_arm(a):
+    import torch
+    import torch.distributed as dist
+
+    from easydl_b200 import _lib
+    from easydl_b200.criteo import CriteoSynthetic
+    from easydl_b200.optimizer import OptimizerSpec
+    from easydl_b200.parameters import ShardParameters
+
+    _lib.load()  # no fallback: raises if the CUDA extension is missing
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != a.gpus:
+        if world == 1 and a.gpus > 1:
+            raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run (one rank per GPU)")
+    dev = torch.device(f"cuda:{local_rank}")
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    rows = [a.rows] * N_FIELDS
+    opt = OptimizerSpec.adagrad() if a.optimizer == "adagrad" else OptimizerSpec.adam()
+    D, B, F = a.dim, a.batch, N_FIELDS
+    N = B * F
+    params = ShardParameters(rows, D, opt, world, rank, device=dev)
+
+    if world == 1:
+        from easydl_b200.step import SparseStep
+        step = SparseStep(params, B)
+    else:
+        from easydl_b200.sharded_step import ShardedSparseStep
+        from easydl_b200.exchange import TorchExchange
+        step = ShardedSparseStep(params, B, TorchExchange(dist.group.WORLD, dev))
+
+    # distinct batches per rank: step index = batch_no * world + rank
+    src = CriteoSynthetic(rows, B, a.alpha)
+    nb = max(1, a.n_batches)
+    ids_host = [torch.from_numpy(src.ids(i * world + rank)).pin_memory() for i in range(nb)]
+    grad_host = torch.from_numpy(src.grad(D, rank)).pin_memory()
+    ids_dev = [t.to(dev) for t in ids_host]
+    grad_dev = grad_host.to(dev)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+
+    # ---------------- device-resident timed region
+    for i in range(a.warmup):
+        step.run(ids_dev[i % nb], grad_dev)
+    barrier()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(a.steps)]
+    t_begin = torch.cuda.Event(enable_timing=True)
+    t_end = torch.cuda.Event(enable_timing=True)
+    n_u_acc = torch.zeros(1, dtype=torch.int64, device=dev)
+    if sampler:
+        sampler.active = True
+    t_begin.record()
+    for i in range(a.steps):
+        ids = ids_dev[(a.warmup + i) % nb]
+        if world == 1:
+            ev[i][0].record()
+            step.lookup(ids)
+            ev[i][1].record()
+            uq = step.dedup(ids)
+            ev[i][2].record()
+            step.update(ids, grad_dev, uq)
+            ev[i][3].record()
+            n_u_acc += uq.n_unique
+        else:
+            step.run(ids, grad_dev)
+            n_u_acc += step.last_n_unique
+    t_end.record()
+    barrier()
+    if sampler:
+        sampler.active = False
+    ms = t_begin.elapsed_time(t_end)
+    t_ms = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+    ms_max = float(t_ms.item())
+    value = B * world * a.steps / (ms_max * 1e-3)
+    U_mean = float(n_u_acc.item()) / a.steps
+
+    phases = None
+    if world == 1:
+        lk = [e[0].elapsed_time(e[1]) for e in ev]
+        dd = [e[1].elapsed_time(e[2]) for e in ev]
+        up = [e[2].elapsed_time(e[3]) for e in ev]
+        phases = {"lookup_ms": statistics.mean(lk), "dedup_ms": statistics.mean(dd),
+                  "update_ms": statistics.mean(up)}
+
+    # ---------------- end-to-end through the host-buffer PS API
+    e2e = None
+    if not a.no_e2e:
+        from easydl_b200.ps_client import HostStepRunner
+        runner = HostStepRunner(step, dev)
+        for i in range(2):
+            runner.run(ids_host[i % nb], grad_host)
+        barrier()
+        if sampler:
+            sampler.active = True
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(a.e2e_steps):
+            runner.run(ids_host[i % nb], grad_host)
+        e1.record()
+        barrier()
+        if sampler:
+            sampler.active = False
+        t2 = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        e2e = {"value": B * world * a.e2e_steps / (float(t2.item()) * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": runner.h2d_bytes, "d2h_bytes_per_step": runner.d2h_bytes,
+               "ms_per_step": float(t2.item()) / a.e2e_steps,
+               "path": "HostStepRunner: ids H2D -> lookup -> emb D2H -> grad H2D -> dedup + update -> n_unique D2H"}
+
+    clocks = sampler.result() if sampler else None
+
+    if rank == 0:
+        peak, peak_kind = measured_peak_gbs()
+        lookup_b, update_b = algorithmic_bytes(N, U_mean, D, a.optimizer)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": ms_max / a.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(a), "global_batch": B * world,
+                       "tables": F, "rows_per_table": a.rows, "dim": D, "zipf_alpha": a.alpha,
+                       "unique_per_step": U_mean, "sharding": f"row-wise id mod {world}",
+                       "cache": "inputs larger than L2: 133 GB of table rows touched at random, "
+                                f"{nb} id batches cycled, 436 MB gradient + 436 MB output per step"},
+            "gpu_launches": step.launches_per_step * a.steps,
+            "clocks": clocks,
+        }
+        if phases:
+            t_up = phases["update_ms"] * 1e-3
+            t_lk = phases["lookup_ms"] * 1e-3
+            ach = update_b / t_up / 1e9
+            line["roofline"] = {
+                "kernel": "k_seg_short + k_seg_long (segmented reduce + Adagrad row update)",
+                "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": None, "peak_kind": peak_kind,
+                "algorithmic_bytes_per_launch": update_b,
+            }
+            line["phases"] = dict(phases)
+            line["phases"]["lookup_gbs"] = lookup_b / t_lk / 1e9
+            line["phases"]["lookup_frac"] = lookup_b / t_lk / 1e9 / peak
+            line["phases"]["lookup_update_gbs_whole_step"] = (lookup_b + update_b) / (ms_max / a.steps * 1e-3) / 1e9
+        if e2e:
+            line["e2e"] = e2e
+        if not a.no_cpu_baseline:
+            v, spp = cpu_reference(a, 1, a.cpu_steps, 1)
+            line["cpu_baseline"] = {
+                "value": v, "unit": UNIT, "cores": 1, "kind": "port",
+                "sample": f"{a.cpu_steps} full steps of the same workload through the NumPy oracle "
+                          f"(1 thread; {os.cpu_count()} cores present), rows pre-materialised",
+                "ms_per_step": spp * 1e3}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference_arm(a)
+    else:
+        run_b200_arm(a)
+
+
+if __name__ == "__main__":
+    main()

@@ -40,8 +40,8 @@ class SparseStep:
                                      dtype=torch.uint8, device=dev)
         self.ws_seg = torch.empty(lib.edl_segreduce_workspace_bytes(N, D), dtype=torch.uint8, device=dev)
         # launches per step (for bench.py's gpu_launches): gather 1; unique 3/pass + 3; update 2 + memset
-        self.launches_lookup = 1
-        self.launches_update = 3 * ((self.key_bits + 7) // 8) + 3 + 2
+        self.launches_per_step = 1 + 3 * ((self.key_bits + 7) // 8) + 3 + 2
+        self.last_n_unique = self.uq.n_unique
 
     def lookup(self, ids: torch.Tensor) -> torch.Tensor:
         """ids int64 [B, F] on the device -> emb [B*F, dim]."""

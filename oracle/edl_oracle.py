@@ -141,15 +141,34 @@ def partition_mod(keys: np.ndarray, bases: np.ndarray, num_shards: int):
 
 
 # --------------------------------------------------------------------------- A4
-def segment_sum_f64(grad: np.ndarray, order: np.ndarray, seg: np.ndarray) -> np.ndarray:
-    """A4: g_uniq[u] = sum of grad rows of segment u, accumulated in float64 and
-    rounded once to fp32.  SPEC 'A4 gradient reduce'."""
+def segment_sum_f64_reduceat(grad: np.ndarray, order: np.ndarray, seg: np.ndarray) -> np.ndarray:
+    """A4, definitional form: np.add.reduceat over the float64 copy of the sorted rows."""
     n_u = len(seg) - 1
     if n_u == 0:
         return np.zeros((0, grad.shape[1]), dtype=np.float32)
     g64 = grad[order].astype(np.float64)
     out = np.add.reduceat(g64, seg[:-1].astype(np.int64), axis=0)
     return out.astype(np.float32)
+
+
+def segment_sum_f64(grad: np.ndarray, order: np.ndarray, seg: np.ndarray) -> np.ndarray:
+    """A4: g_uniq[u] = sum of grad rows of segment u, accumulated in float64 and
+    rounded once to fp32.  SPEC 'A4 gradient reduce'.
+
+    Same sums as segment_sum_f64_reduceat, evaluated as a CSR (U x N, all ones) times dense
+    product in float64 when SciPy is present: its C loop adds the rows of a segment left to
+    right, 20x faster than reduceat over axis 0, which matters for the timed CPU baseline."""
+    n_u = len(seg) - 1
+    if n_u == 0:
+        return np.zeros((0, grad.shape[1]), dtype=np.float32)
+    try:
+        from scipy.sparse import csr_matrix
+    except ImportError:  # pragma: no cover
+        return segment_sum_f64_reduceat(grad, order, seg)
+    n = len(order)
+    m = csr_matrix((np.ones(n, dtype=np.float64), order.astype(np.int32), seg.astype(np.int32)),
+                   shape=(n_u, grad.shape[0]))
+    return np.asarray(m @ grad.astype(np.float64)).astype(np.float32)
 
 
 # --------------------------------------------------------------------------- A5
@@ -289,12 +308,17 @@ class OracleShard:
         return out
 
     # -- A5
-    def apply(self, uniq: np.ndarray, g_uniq: np.ndarray):
-        """Sparse optimizer step on rows `uniq` (ascending, unique, owned by this shard)."""
-        self.step += 1
+    def apply(self, uniq: np.ndarray, g_uniq: np.ndarray, bump_step: bool = True,
+              materialise: bool = True):
+        """Sparse optimizer step on rows `uniq` (ascending, unique, owned by this shard).
+        bump_step=False / materialise=False let a per-table driver call this once per table
+        inside one global step, on rows that already exist (disjoint in-place updates)."""
+        if bump_step:
+            self.step += 1
         if len(uniq) == 0:
             return
-        self.materialise(uniq)
+        if materialise:
+            self.materialise(uniq)
         pos = np.searchsorted(self.keys, uniq)
         if self.opt.kind == ADAGRAD:
             p, acc = adagrad_rows(self.w[pos], self.slots[0][pos], g_uniq,
@@ -325,6 +349,33 @@ def sparse_step(shard: OracleShard, keys: np.ndarray, grad: np.ndarray):
     g_uniq = segment_sum_f64(grad, order, seg)
     shard.apply(uniq, g_uniq)
     return emb, (uniq, inverse, counts, order, seg), g_uniq
+
+
+def sparse_step_per_table(shard: OracleShard, ids: np.ndarray, grad: np.ndarray, pool=None):
+    """The same step as sparse_step, one table at a time (tables are independent), optionally
+    on a thread pool: NumPy releases the GIL inside sort / take / ufunc loops, so this is the
+    multi-core form of the CPU parameter-server path used by bench.py --impl reference.
+    ids[B, F] per-table ids, grad[B*F, D].  Rows must already be materialised when pool is
+    given (threads then only update disjoint slices in place)."""
+    B, F = ids.shape
+    D = shard.dim
+    g3 = grad.reshape(B, F, D)
+    emb = np.empty((B, F, D), dtype=np.float32)
+    shard.step += 1
+
+    def one(t):
+        keys = ids[:, t] + shard.bases[t]
+        uniq, inverse, counts, order, seg = dedup(keys)
+        emb[:, t, :] = shard.lookup(uniq)[inverse]
+        g_uniq = segment_sum_f64(np.ascontiguousarray(g3[:, t, :]), order, seg)
+        shard.apply(uniq, g_uniq, bump_step=False, materialise=pool is None)
+        return len(uniq)
+
+    if pool is None:
+        n_u = [one(t) for t in range(F)]
+    else:
+        n_u = list(pool.map(one, range(F)))
+    return emb.reshape(B * F, D), int(sum(n_u))
 
 
 def sharded_step(shards: List[OracleShard], keys_per_worker: List[np.ndarray],
