@@ -494,3 +494,74 @@ extern "C" int edl_partition_mod(const int64_t* keys, int64_t n, const int32_t* 
   EDL_LAUNCH_CHECK("partition kernels");
   return EDL_OK;
 }
+
+// --------------------------------------------------------------- A1 without any allocation
+// edl_unique_static: the same dedup as edl_unique, but the scratch it needs lives in a fixed
+// array that is part of the library image instead of a caller-provided workspace.
+//
+// The array below is DEVICE memory.  Inside host functions its name is only a handle the
+// CUDA runtime understands -- it is not a device address and must never be handed to a kernel
+// as a pointer.  The real address is asked for once per device with cudaGetSymbolAddress
+// (with that device current) and cached in g_static_addr[].
+#include <mutex>
+
+static __device__ __align__(256) unsigned char g_unique_scratch[EDL_UNIQUE_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+void* g_static_addr[kMaxDevices] = {nullptr};
+
+// Resolves the device address of g_unique_scratch on the current device (first call only).
+int static_scratch(void** out) {
+  int dev = -1;
+  EDL_CUDA(cudaGetDevice(&dev));
+  EDL_REQUIRE(dev >= 0 && dev < kMaxDevices, EDL_ELIMIT, "edl_unique_static: device ordinal %d beyond %d",
+              dev, kMaxDevices);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_addr[dev]) {
+    void* p = nullptr;
+    EDL_CUDA(cudaGetSymbolAddress(&p, g_unique_scratch));
+    EDL_REQUIRE(p != nullptr, EDL_ECUDA, "edl_unique_static: cudaGetSymbolAddress returned a null address");
+    g_static_addr[dev] = p;
+  }
+  *out = g_static_addr[dev];
+  return EDL_OK;
+}
+}  // namespace
+
+extern "C" int edl_unique_static(const int64_t* ids, int64_t n, const int32_t* n_dev,
+                                 const int64_t* field_base, int n_fields, int key_bits,
+                                 int64_t* uniq, int32_t* inverse, int32_t* counts, int32_t* order,
+                                 int32_t* seg_offsets, int32_t* n_unique, edl_stream_t stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  EDL_REQUIRE(n >= 0, EDL_EINVAL, "edl_unique_static: n=%lld negative", (long long)n);
+  EDL_REQUIRE(n <= (int64_t)EDL_UNIQUE_STATIC_MAX_IDS, EDL_ELIMIT,
+              "edl_unique_static: n=%lld exceeds the built-in scratch limit of %d ids; use edl_unique "
+              "with a caller-provided workspace for larger batches",
+              (long long)n, EDL_UNIQUE_STATIC_MAX_IDS);
+  EDL_REQUIRE(key_bits >= 1 && key_bits <= 64, EDL_EINVAL, "edl_unique_static: key_bits=%d not in 1..64", key_bits);
+  EDL_REQUIRE(seg_offsets && n_unique, EDL_EINVAL, "edl_unique_static: seg_offsets and n_unique are required");
+  EDL_REQUIRE(!field_base || n_fields > 0, EDL_EINVAL, "edl_unique_static: n_fields must be > 0 with field_base");
+  if (n == 0) {
+    k_empty_unique<<<1, 1, 0, st>>>(n_unique, seg_offsets);
+    EDL_LAUNCH_CHECK("k_empty_unique");
+    return EDL_OK;
+  }
+  EDL_REQUIRE(ids && uniq && order, EDL_EINVAL, "edl_unique_static: ids, uniq and order are required");
+  void* scratch = nullptr;
+  int rc = static_scratch(&scratch);
+  if (rc) return rc;
+  UniqueWs W = carve_unique(scratch, n, key_bits);
+  EDL_REQUIRE(W.bytes <= (size_t)EDL_UNIQUE_STATIC_SCRATCH_BYTES, EDL_ELIMIT,
+              "edl_unique_static: n=%lld at key_bits=%d needs %zu scratch bytes, the built-in array has %d",
+              (long long)n, key_bits, W.bytes, EDL_UNIQUE_STATIC_SCRATCH_BYTES);
+  // Nothing in the scratch has to start at zero: every histogram cell, digit total and tile
+  // count is written by this call before this call reads it, so whatever the previous call
+  // left behind is never observed.
+  if (key_bits <= 32)
+    return unique_impl<uint32_t>(ids, n, n_dev, field_base, n_fields, key_bits, uniq, inverse, counts,
+                                 order, seg_offsets, n_unique, W, st);
+  return unique_impl<uint64_t>(ids, n, n_dev, field_base, n_fields, key_bits, uniq, inverse, counts,
+                               order, seg_offsets, n_unique, W, st);
+}

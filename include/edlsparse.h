@@ -78,6 +78,36 @@ int edl_unique(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64_
                int32_t* order, int32_t* seg_offsets, int32_t* n_unique, void* workspace,
                size_t workspace_bytes, edl_stream_t stream);
 
+/* ---- A1 for callers that cannot allocate device memory -----------------------------------
+ * No counterpart in the reference (nor in the ElasticDL lineage): added for this library's
+ * own users.  Same inputs, outputs and results as edl_unique, but no workspace argument: the
+ * scratch is a fixed EDL_UNIQUE_STATIC_SCRATCH_BYTES array inside the library image, so the
+ * call reaches no cudaMalloc / cudaFree and no allocating routine of any other library.
+ *
+ * Who needs it: a parameter-server process whose tables were sized to fill the GPU (a raw
+ * allocation may simply fail once 180 GB are spoken for); a C/C++ host that lives inside a
+ * framework whose caching allocator owns all device memory and is not reachable from here;
+ * and latency-critical serving threads, for which an allocation's implicit device-wide
+ * synchronisation stalls every stream of the process.
+ *
+ * Limits and rules
+ *   - n <= EDL_UNIQUE_STATIC_MAX_IDS (131072 ids, e.g. a 4096-sample x 26-field batch) and the
+ *     scratch the call would need must fit the array; beyond that the call returns
+ *     EDL_ELIMIT with a message and does nothing.  Use edl_unique for larger batches.
+ *   - The array costs EDL_UNIQUE_STATIC_SCRATCH_BYTES of device memory on every GPU that loads
+ *     the library, until the process exits.
+ *   - The first call on each device looks the array's device address up (cudaGetSymbolAddress,
+ *     with that device current).  Make that first call before starting any stream capture.
+ *   - All calls on a device share the one array.  It still holds the previous call's data;
+ *     the call never depends on it (every scratch word is written before it is read).
+ *     Two calls that can overlap on the GPU (different streams, no ordering between them)
+ *     race on the scratch and produce garbage: serialise them. */
+#define EDL_UNIQUE_STATIC_MAX_IDS 131072
+#define EDL_UNIQUE_STATIC_SCRATCH_BYTES (3 * 1024 * 1024)
+int edl_unique_static(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64_t* field_base,
+                      int n_fields, int key_bits, int64_t* uniq, int32_t* inverse, int32_t* counts,
+                      int32_t* order, int32_t* seg_offsets, int32_t* n_unique, edl_stream_t stream);
+
 /* ---- A2 hash-mod partition (lineage int_to_id / scatter_embedding_vector) --------------
  * Stable partition of keys[0..n) by (per-table id mod S'), S' = num_shards (1..256), tables
  * located through `layout` (only T and key_base are read; NULL = single table, id == key).
