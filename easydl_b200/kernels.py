@@ -205,20 +205,24 @@ def scatter_rows(rows: torch.Tensor, pos: torch.Tensor, out: torch.Tensor, *,
 # ------------------------------------------------------------------------------- A4 / A5
 def segreduce(grad: torch.Tensor, order: torch.Tensor, seg_offsets: torch.Tensor,
               n_unique: torch.Tensor, max_unique: int, *, out_pos: Optional[torch.Tensor] = None,
-              out: Optional[torch.Tensor] = None, workspace: Optional[torch.Tensor] = None):
+              out: Optional[torch.Tensor] = None, out_dtype=torch.float32,
+              workspace: Optional[torch.Tensor] = None):
+    """g[dst(u)] = float64 segment sum; out_dtype float32 (rounded once) or float64 (exact wire)."""
     lib = _lib.load()
     _need(grad, torch.float32, "grad")
     _need(order, torch.int32, "order")
     _need(seg_offsets, torch.int32, "seg_offsets")
     dim = grad.shape[1]
     if out is None:
-        out = torch.empty((max_unique, dim), dtype=torch.float32, device=grad.device)
+        out = torch.empty((max_unique, dim), dtype=out_dtype, device=grad.device)
+    if out.dtype not in (torch.float32, torch.float64):
+        raise TypeError("segreduce output must be float32 or float64")
     need = lib.edl_segreduce_workspace_bytes(max_unique, dim)
     if workspace is None or workspace.numel() < need:
         workspace = _ws(need, grad.device)
     check(lib.edl_segreduce(_ptr(grad), dim, _ptr(order), _ptr(seg_offsets), _ptr(n_unique),
-                            max_unique, _ptr(out_pos), _ptr(out), _ptr(workspace),
-                            workspace.numel(), _stream()), "edl_segreduce")
+                            max_unique, _ptr(out_pos), _ptr(out), int(out.dtype == torch.float64),
+                            _ptr(workspace), workspace.numel(), _stream()), "edl_segreduce")
     return out
 
 
@@ -228,10 +232,13 @@ def segreduce_update(slab: torch.Tensor, slot0: torch.Tensor, slot1: Optional[to
                      layout: Optional[torch.Tensor], opt: OptParams,
                      touched: Optional[torch.Tensor] = None,
                      workspace: Optional[torch.Tensor] = None):
+    """grad rows may be float32 (a worker's raw gradient) or float64 (exchanged partial sums)."""
     lib = _lib.load()
     _need(slab, torch.float32, "slab")
     _need(slot0, torch.float32, "slot0")
-    _need(grad, torch.float32, "grad")
+    if grad.dtype not in (torch.float32, torch.float64):
+        raise TypeError("grad must be float32 or float64")
+    _need(grad, grad.dtype, "grad")
     _need(uniq, torch.int64, "uniq")
     dim = slab.shape[1]
     if grad.shape[1] != dim:
@@ -241,9 +248,9 @@ def segreduce_update(slab: torch.Tensor, slot0: torch.Tensor, slot1: Optional[to
         workspace = _ws(need, slab.device)
     check(lib.edl_segreduce_update(_ptr(slab), _ptr(slot0), _ptr(slot1), dim, _ptr(uniq),
                                    _ptr(order), _ptr(seg_offsets), _ptr(n_unique), max_unique,
-                                   _ptr(grad), _ptr(layout), C.byref(opt), _ptr(touched),
-                                   _ptr(workspace), workspace.numel(), _stream()),
-          "edl_segreduce_update")
+                                   _ptr(grad), int(grad.dtype == torch.float64), _ptr(layout),
+                                   C.byref(opt), _ptr(touched), _ptr(workspace), workspace.numel(),
+                                   _stream()), "edl_segreduce_update")
 
 
 # ------------------------------------------------------------------------------- A6

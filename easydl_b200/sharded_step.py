@@ -21,7 +21,12 @@ from .parameters import ShardParameters
 
 class ShardedSparseStep:
     def __init__(self, params: ShardParameters, batch_size: int, exchange=None,
-                 n_fields: Optional[int] = None):
+                 n_fields: Optional[int] = None, wire_dtype=torch.float64):
+        # wire_dtype: element type of the per-worker partial gradient sums on the wire.
+        # float64 (default) keeps the owner's total equal to one float64 pass over the global
+        # batch (SPEC A4: independent of S and of the worker split); float32 halves the
+        # gradient exchange bytes at the cost of one extra fp32 rounding per worker.
+        self.wire_dtype = wire_dtype
         self.params = params
         self.S = params.num_shards
         self.rank = params.shard
@@ -63,7 +68,7 @@ class ShardedSparseStep:
 
     def gen_update(self, grad: torch.Tensor) -> Generator:
         uq, part, send, recv, recv_keys, U = self._fw
-        g_send = torch.empty((max(U, 1), self.params.dim), dtype=torch.float32, device=grad.device)
+        g_send = torch.empty((max(U, 1), self.params.dim), dtype=self.wire_dtype, device=grad.device)
         K.segreduce(grad, uq.order, uq.seg_offsets, uq.n_unique, uq.n, out_pos=part.pos, out=g_send)
         g_recv = yield ("a2av", g_send[:U], send, recv)      # aligned with recv_keys
         R = recv_keys.numel()

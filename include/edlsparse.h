@@ -136,16 +136,22 @@ int edl_compose_index(const int32_t* index, const int32_t* map, int64_t n, int32
 
 /* ---- A4 segmented gradient reduce (lineage deduplicate_indexed_slices, sum half) -------
  * g_out[dst(u)] = sum over i in [seg_offsets[u], seg_offsets[u+1]) of grad[order[i]],
- * accumulated in float64, rounded once to fp32.  dst(u) = out_pos ? out_pos[u] : u.
+ * accumulated in float64.  dst(u) = out_pos ? out_pos[u] : u.
+ * out_f64 == 0: g_out is float[.., dim], the sum rounded once to fp32.
+ * out_f64 != 0: g_out is double[.., dim], the float64 partial sums themselves -- the exact
+ *               wire format of the worker -> PS gradient exchange (the owner's total is then
+ *               independent of how the batch was split over workers, up to float64 rounding).
  * n_unique_dev: device int32 U; max_unique: host upper bound. */
 size_t edl_segreduce_workspace_bytes(int64_t max_unique, int dim);
 int edl_segreduce(const float* grad, int dim, const int32_t* order, const int32_t* seg_offsets,
                   const int32_t* n_unique_dev, int64_t max_unique, const int32_t* out_pos,
-                  float* g_out, void* workspace, size_t workspace_bytes, edl_stream_t stream);
+                  void* g_out, int out_f64, void* workspace, size_t workspace_bytes,
+                  edl_stream_t stream);
 
 /* ---- A4 + A5 fused: reduce, then optimizer row update in place (lineage PS
  * push_gradients -> optimizer kernel) -------------------------------------------------------
- * For each unique u: g = segment sum as above; row = row(uniq[u]) through layout;
+ * For each unique u: g = segment sum as above (grad rows are float, or double when
+ * grad_f64 != 0), rounded once to fp32; row = row(uniq[u]) through layout;
  * Adagrad: acc += g*g; p -= lr*g/(sqrt(acc)+eps)                       (slot0 = acc)
  * Adam   : m = b1*m+(1-b1)*g; v = b2*v+((1-b2)*g)*g; p -= lr_t*m/(sqrt(v)+eps)
  *          (slot0 = m, slot1 = v; lr_t computed by the caller in float64)
@@ -161,9 +167,10 @@ typedef struct edl_opt_params {
 
 int edl_segreduce_update(float* slab, float* slot0, float* slot1, int dim, const int64_t* uniq,
                          const int32_t* order, const int32_t* seg_offsets,
-                         const int32_t* n_unique_dev, int64_t max_unique, const float* grad,
-                         const int64_t* layout, const edl_opt_params* opt_host, uint32_t* touched,
-                         void* workspace, size_t workspace_bytes, edl_stream_t stream);
+                         const int32_t* n_unique_dev, int64_t max_unique, const void* grad,
+                         int grad_f64, const int64_t* layout, const edl_opt_params* opt_host,
+                         uint32_t* touched, void* workspace, size_t workspace_bytes,
+                         edl_stream_t stream);
 
 /* ---- A6 elastic re-shard (lineage CheckpointSaver / restore_params_from_checkpoint) ----
  * edl_export_count : n_out (device int32) = number of set bits in touched[0..n_rows).

@@ -29,10 +29,11 @@ def _make(cuda, rows, dim, S, opt_name):
     return params, po, oo
 
 
-def _train(cuda, params, oshards, rows, dim, batch, steps, alpha, step0=0):
+def _train(cuda, params, oshards, rows, dim, batch, steps, alpha, step0=0, fresh=None):
     from easydl_b200.exchange import run_lockstep
     from easydl_b200.sharded_step import ShardedSparseStep
     S = len(params)
+    fresh = (step0 == 0) if fresh is None else fresh
     bases = O.key_bases(rows)
     st = [ShardedSparseStep(p, batch) for p in params]
     for k in range(steps):
@@ -46,7 +47,13 @@ def _train(cuda, params, oshards, rows, dim, batch, steps, alpha, step0=0):
         embs = run_lockstep(gens)
         want = O.sharded_step(oshards, kw, gw)
         for r in range(S):
-            assert np.array_equal(bits(embs[r].cpu().numpy()), bits(want[r])), f"emb step {k} rank {r}"
+            got = embs[r].cpu().numpy()
+            if fresh and k == 0:   # nothing updated yet: the lookup is pure data movement
+                assert np.array_equal(bits(got), bits(want[r])), f"emb step {k} rank {r}"
+            # later lookups read rows the GPU updated itself: per-worker fp32 partial sums are
+            # merged by the owner, the oracle does one float64 pass (SPEC A4) -> tolerance
+            err = np.abs(got.astype(np.float64) - want[r])
+            assert np.all(err <= ATOL + RTOL * np.abs(want[r])), f"emb step {k} rank {r}: {err.max():.3e}"
 
 
 def _compare_state(cuda, params, oshards, n_slots, exact_floor=0.98):
