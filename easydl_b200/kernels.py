@@ -217,11 +217,12 @@ def segreduce(grad: torch.Tensor, order: torch.Tensor, seg_offsets: torch.Tensor
         out = torch.empty((max_unique, dim), dtype=out_dtype, device=grad.device)
     if out.dtype not in (torch.float32, torch.float64):
         raise TypeError("segreduce output must be float32 or float64")
-    need = lib.edl_segreduce_workspace_bytes(max_unique, dim)
+    n_rows = grad.shape[0]
+    need = lib.edl_segreduce_workspace_bytes(max_unique, n_rows, dim)
     if workspace is None or workspace.numel() < need:
         workspace = _ws(need, grad.device)
     check(lib.edl_segreduce(_ptr(grad), dim, _ptr(order), _ptr(seg_offsets), _ptr(n_unique),
-                            max_unique, _ptr(out_pos), _ptr(out), int(out.dtype == torch.float64),
+                            max_unique, n_rows, _ptr(out_pos), _ptr(out), int(out.dtype == torch.float64),
                             _ptr(workspace), workspace.numel(), _stream()), "edl_segreduce")
     return out
 
@@ -243,12 +244,13 @@ def segreduce_update(slab: torch.Tensor, slot0: torch.Tensor, slot1: Optional[to
     dim = slab.shape[1]
     if grad.shape[1] != dim:
         raise ValueError("grad and slab dims differ")
-    need = lib.edl_segreduce_workspace_bytes(max_unique, dim)
+    n_rows = grad.shape[0]
+    need = lib.edl_segreduce_workspace_bytes(max_unique, n_rows, dim)
     if workspace is None or workspace.numel() < need:
         workspace = _ws(need, slab.device)
     check(lib.edl_segreduce_update(_ptr(slab), _ptr(slot0), _ptr(slot1), dim, _ptr(uniq),
                                    _ptr(order), _ptr(seg_offsets), _ptr(n_unique), max_unique,
-                                   _ptr(grad), int(grad.dtype == torch.float64), _ptr(layout),
+                                   n_rows, _ptr(grad), int(grad.dtype == torch.float64), _ptr(layout),
                                    C.byref(opt), _ptr(touched), _ptr(workspace), workspace.numel(),
                                    _stream()), "edl_segreduce_update")
 

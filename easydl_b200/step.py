@@ -38,9 +38,9 @@ class SparseStep:
             n_unique=torch.zeros(1, dtype=torch.int32, device=dev), n=N)
         self.ws_unique = torch.empty(lib.edl_unique_workspace_bytes(N, self.key_bits),
                                      dtype=torch.uint8, device=dev)
-        self.ws_seg = torch.empty(lib.edl_segreduce_workspace_bytes(N, D), dtype=torch.uint8, device=dev)
+        self.ws_seg = torch.empty(lib.edl_segreduce_workspace_bytes(N, N, D), dtype=torch.uint8, device=dev)
         # launches per step (for bench.py's gpu_launches): gather 1; unique 3/pass + 3; update 2 + memset
-        self.launches_per_step = 1 + 3 * ((self.key_bits + 7) // 8) + 3 + 2
+        self.launches_per_step = 1 + 3 * ((self.key_bits + 7) // 8) + 3 + 3  # + one memset node
         self.last_n_unique = self.uq.n_unique
 
     def lookup(self, ids: torch.Tensor) -> torch.Tensor:
@@ -61,3 +61,40 @@ class SparseStep:
         emb = self.lookup(ids)
         self.update(ids, grad)
         return emb
+
+
+class GraphedStep:
+    """A SparseStep captured into CUDA graphs for one fixed (ids, grad) buffer pair: the 17
+    launches of a step cost one graph launch instead of 17 trips through the driver.  Three
+    graphs (lookup / dedup / update) so that a caller can time the phases with events between
+    them, plus one graph of the whole step.  Adagrad only: Adam's bias-corrected rate changes
+    every step and is a by-value kernel argument."""
+
+    def __init__(self, step: SparseStep, ids: torch.Tensor, grad: torch.Tensor):
+        from ._lib import EDL_OPT_ADAGRAD
+        if step.params.opt.kind != EDL_OPT_ADAGRAD:
+            raise ValueError("GraphedStep supports Adagrad only")
+        self.step, self.ids, self.grad = step, ids, grad
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):   # warm-up outside capture (sets function attributes)
+            step.run(ids, grad)
+        cur.wait_stream(side)
+        torch.cuda.synchronize()
+        self.g_lookup, self.g_dedup, self.g_update, self.g_all = (torch.cuda.CUDAGraph() for _ in range(4))
+        host_step = step.params.step   # capture records launches without running them
+        with torch.cuda.graph(self.g_lookup):
+            step.lookup(ids)
+        with torch.cuda.graph(self.g_dedup):
+            step.dedup(ids)
+        with torch.cuda.graph(self.g_update):
+            step.update(ids, grad, step.uq)
+        with torch.cuda.graph(self.g_all):
+            step.run(ids, grad)
+        step.params.step = host_step
+
+    def run(self):
+        self.g_all.replay()
+        self.step.params.step += 1
+        return self.step.emb
