@@ -37,8 +37,8 @@ PROTOTYPES = {
     "edl_init_rows": (_int, [_p, _int, _p, _i64, _i64, C.c_uint64, _p]),
     "edl_fill_f32": (_int, [_p, _i64, C.c_float, _p]),
     "edl_unique_workspace_bytes": (_sz, [_i64, _int]),
-    "edl_unique": (_int, [_p, _i64, _p, _p, _int, _int, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
-    "edl_unique_static": (_int, [_p, _i64, _p, _p, _int, _int, _p, _p, _p, _p, _p, _p, _p]),
+    "edl_unique": (_int, [_p, _i64, _p, _p, _int, _int, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "edl_unique_static": (_int, [_p, _i64, _p, _p, _int, _int, _p, _p, _p, _p, _p, _p, _p, _p]),
     "edl_partition_mod_workspace_bytes": (_sz, [_i64, _int]),
     "edl_partition_mod": (_int, [_p, _i64, _p, _p, _int, _p, _p, _p, _p, _p, _sz, _p]),
     "edl_gather_keys": (_int, [_p, _int, _p, _i64, _p, _p, _p, _p]),
@@ -46,8 +46,8 @@ PROTOTYPES = {
     "edl_expand": (_int, [_p, _int, _p, _i64, _p, _p]),
     "edl_compose_index": (_int, [_p, _p, _i64, _p, _p]),
     "edl_segreduce_workspace_bytes": (_sz, [_i64, _i64, _int]),
-    "edl_segreduce": (_int, [_p, _int, _p, _p, _p, _i64, _i64, _p, _p, _int, _p, _sz, _p]),
-    "edl_segreduce_update": (_int, [_p, _p, _p, _int, _p, _p, _p, _p, _i64, _i64, _p, _int, _p,
+    "edl_segreduce": (_int, [_p, _int, _p, _p, _p, _p, _i64, _i64, _p, _p, _int, _p, _sz, _p]),
+    "edl_segreduce_update": (_int, [_p, _p, _p, _int, _p, _p, _p, _p, _p, _i64, _i64, _p, _int, _p,
                                     C.POINTER(OptParams), _p, _p, _sz, _p]),
     "edl_export_workspace_bytes": (_sz, [_i64]),
     "edl_export_count": (_int, [_p, _i64, _p, _p, _sz, _p]),

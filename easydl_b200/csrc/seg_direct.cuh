@@ -1,30 +1,31 @@
 // Register-path segmented reduce + optimizer: one lane group (dim/4 lanes) per unique id, rows
 // read straight from global memory with kUnrollD loads in flight, thousands of groups resident
 // per SM.  Hot ids (more than kLongThr gradient rows) are cut into kChunk-row chunks that are
-// summed by separate lane groups into float64 partial rows and combined, in chunk order, by one
-// group per hot id -- balanced under any Zipf skew and deterministic.  Included by update.cu.
+// summed by separate lane groups (k_seg_chunk) -- balanced under any Zipf skew and deterministic.  Included by update.cu.
 #pragma once
 #include "seg_common.cuh"
 
 namespace {
 
-constexpr int kLongThr = 32;   // segments longer than this go through the chunk path
+constexpr int kLongThr = 16;   // segments longer than this go through the chunk path
 constexpr int kChunk = 64;     // gradient rows per chunk
 constexpr int kUnrollD = 4;    // independent row loads in flight per lane group (short path)
-constexpr int kUnrollC = 8;    // same, chunk path
+constexpr int kUnrollC = 4;    // same, chunk path
 
 struct DirectWs {
   int32_t* counters;    // [0] long segments, [1] chunks           (cleared before every call)
-  int32_t* long_list;   // [max_long][3]  u, first chunk, n chunks
-  int32_t* chunk_list;  // [max_chunks][2] u, chunk index inside the segment
+  int32_t* long_list;   // [max_long][4]  u, first chunk, n chunks, chunks done
+  int32_t* chunk_list;  // [max_chunks][2] long-list index, chunk index inside the segment
   double* partial;      // [max_chunks][dim]
   int64_t max_long, max_chunks;
 };
 
-template <int kG, int kC, typename GT, typename Epi>
-__global__ void __launch_bounds__(kThreads)
+// kMode: 0 every segment; 1 only ids that occur once; 2 only ids that occur more than once
+template <int kG, int kC, typename GT, typename Epi, int kMinBlocks = 4, int kUnroll = kUnrollD, int kMode = 0>
+__global__ void __launch_bounds__(kThreads, kMinBlocks)
 k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __restrict__ order,
-             const int32_t* __restrict__ seg, const int32_t* __restrict__ n_unique,
+             const int32_t* __restrict__ seg, const int32_t* __restrict__ seg_first,
+             const int32_t* __restrict__ n_unique,
              const int64_t* __restrict__ uniq, const int64_t* __restrict__ layout, Epi epi,
              int32_t* __restrict__ counters, int32_t* __restrict__ long_list,
              int32_t* __restrict__ chunk_list) {
@@ -37,23 +38,28 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
   const int gl = threadIdx.x % kG;
   if (u >= U) return;
   const int s0 = seg[u], s1 = seg[u + 1];
+  const int j0 = seg_first ? seg_first[u] : -1;   // first gradient row of the id, no extra hop
   const int cnt = s1 - s0;
   const unsigned ROWB_G = (unsigned)D4 * R::kBytes4;
-  if (cnt > kLongThr) {
+  if (kMode == 1 && cnt != 1) return;
+  if (kMode == 2 && cnt == 1) return;
+  if (kMode != 1 && cnt > kLongThr) {
     // hot id: register its chunks (one lane claims the slots, the group fills them)
     const int nch = (cnt + kChunk - 1) / kChunk;
-    int base = 0;
+    int base = 0, li = 0;
     if (gl == 0) {
       base = atomicAdd(&counters[1], nch);
-      const int li = atomicAdd(&counters[0], 1);
-      long_list[li * 3 + 0] = u; long_list[li * 3 + 1] = base; long_list[li * 3 + 2] = nch;
+      li = atomicAdd(&counters[0], 1);
+      long_list[li * 4 + 0] = u; long_list[li * 4 + 1] = base; long_list[li * 4 + 2] = nch;
+      long_list[li * 4 + 3] = 0;   // chunks completed so far
     }
     // broadcast from the group's first lane; only this group's lanes take part
     const unsigned lane = threadIdx.x & 31u;
     const unsigned gmask = kG == 32 ? 0xffffffffu : (((1u << kG) - 1u) << (lane / kG * kG));
     base = __shfl_sync(gmask, base, lane / kG * kG);
+    li = __shfl_sync(gmask, li, lane / kG * kG);
     for (int c = gl; c < nch; c += kG) {
-      chunk_list[(base + c) * 2 + 0] = u;
+      chunk_list[(base + c) * 2 + 0] = li;
       chunk_list[(base + c) * 2 + 1] = c;
     }
     return;
@@ -65,8 +71,8 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
     const int col = gl + c * kG;
     if (col < D4) epi.load(row, D4, col, &p[c], &a0[c], &a1[c]);   // in flight during the reduce
   }
-  if (cnt == 1) {
-    const long long j = order[s0];
+  if (kMode != 2 && cnt == 1) {
+    const long long j = j0 >= 0 ? j0 : order[s0];
 #pragma unroll
     for (int c = 0; c < kC; ++c) {
       const int col = gl + c * kG;
@@ -77,14 +83,14 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
         epi.apply(row, D4, col, R::f32(v), s, p[c], a0[c], a1[c]);
       }
     }
-  } else {
+  } else if (kMode != 1) {
     double acc[kC][4];
 #pragma unroll
     for (int c = 0; c < kC; ++c) acc[c][0] = acc[c][1] = acc[c][2] = acc[c][3] = 0.0;
-    for (int i = s0; i < s1; i += kUnrollD) {
-      typename R::V v[kUnrollD][kC];
+    for (int i = s0; i < s1; i += kUnroll) {
+      typename R::V v[kUnroll][kC];
 #pragma unroll
-      for (int k = 0; k < kUnrollD; ++k) {
+      for (int k = 0; k < kUnroll; ++k) {
         if (i + k < s1) {
           const long long j = order[i + k];
 #pragma unroll
@@ -95,7 +101,7 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
         }
       }
 #pragma unroll
-      for (int k = 0; k < kUnrollD; ++k) {
+      for (int k = 0; k < kUnroll; ++k) {
         if (i + k < s1) {
 #pragma unroll
           for (int c = 0; c < kC; ++c) {
@@ -118,20 +124,30 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
   if (gl == 0) epi.touch(row);
 }
 
-// one lane group per chunk of a hot id: float64 partial row -> scratch
-template <int kG, int kC, typename GT>
-__global__ void __launch_bounds__(kThreads)
+// One lane group per chunk (<= kChunk rows) of a hot id.  An id that fits one chunk is finished
+// here (sum + epilogue).  Longer ids leave a float64 partial row per chunk in scratch for
+// k_seg_long_final.
+template <int kG, int kC, typename GT, typename Epi>
+__global__ void __launch_bounds__(kThreads, 4)
 k_seg_chunk(const unsigned char* __restrict__ grad, int D4, const int32_t* __restrict__ order,
             const int32_t* __restrict__ seg, const int32_t* __restrict__ counters,
-            const int32_t* __restrict__ chunk_list, double* __restrict__ partial) {
+            const int32_t* __restrict__ chunk_list, int32_t* __restrict__ long_list,
+            double* __restrict__ partial, const int64_t* __restrict__ uniq,
+            const int64_t* __restrict__ layout, Epi epi) {
+  __shared__ EdlLayoutSmem L;
   typedef Row<GT> R;
+  edl_layout_load(&L, layout);
+  __syncthreads();
   const int n_chunks = counters[1];
   const int gl = threadIdx.x % kG;
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned gmask = kG == 32 ? 0xffffffffu : (((1u << kG) - 1u) << (lane / kG * kG));
   const int groups = (int)((int64_t)gridDim.x * kThreads / kG);
   const unsigned ROWB_G = (unsigned)D4 * R::kBytes4;
   const int D = D4 * 4;
   for (int ci = (int)(((int64_t)blockIdx.x * kThreads + threadIdx.x) / kG); ci < n_chunks; ci += groups) {
-    const int u = chunk_list[ci * 2], c0 = chunk_list[ci * 2 + 1];
+    const int li = chunk_list[ci * 2], c0 = chunk_list[ci * 2 + 1];
+    const int u = long_list[li * 4], base = long_list[li * 4 + 1], nch = long_list[li * 4 + 2];
     const int b = seg[u] + c0 * kChunk;
     const int e = min(seg[u + 1], b + kChunk);
     double acc[kC][4];
@@ -161,21 +177,37 @@ k_seg_chunk(const unsigned char* __restrict__ grad, int D4, const int32_t* __res
         }
       }
     }
+    if (nch > 1) {
+#pragma unroll
+      for (int c = 0; c < kC; ++c) {
+        const int col = gl + c * kG;
+        if (col < D4) {
+          double2* dst = (double2*)(partial + (size_t)ci * D + col * 4);
+          dst[0] = make_double2(acc[c][0], acc[c][1]);
+          dst[1] = make_double2(acc[c][2], acc[c][3]);
+        }
+      }
+      continue;   // k_seg_long_final adds the partial rows of this id in chunk order
+    }
+    const long long row = epi.row_of(&L, uniq, u);
 #pragma unroll
     for (int c = 0; c < kC; ++c) {
       const int col = gl + c * kG;
       if (col < D4) {
-        double2* dst = (double2*)(partial + (size_t)ci * D + col * 4);
-        dst[0] = make_double2(acc[c][0], acc[c][1]);
-        dst[1] = make_double2(acc[c][2], acc[c][3]);
+        float4 p = make_float4(0, 0, 0, 0), a0 = p, a1 = p;
+        epi.load(row, D4, col, &p, &a0, &a1);
+        float4 g = make_float4(__double2float_rn(acc[c][0]), __double2float_rn(acc[c][1]),
+                               __double2float_rn(acc[c][2]), __double2float_rn(acc[c][3]));
+        epi.apply(row, D4, col, g, acc[c], p, a0, a1);
       }
     }
+    if (gl == 0) epi.touch(row);
   }
 }
 
-// one lane group per hot id: partial rows added in chunk order, then the epilogue
+// one lane group per hot id with more than one chunk: partial rows added in chunk order, epilogue
 template <int kG, int kC, typename Epi>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 4)
 k_seg_long_final(int D4, const int32_t* __restrict__ counters, const int32_t* __restrict__ long_list,
                  const double* __restrict__ partial, const int64_t* __restrict__ uniq,
                  const int64_t* __restrict__ layout, Epi epi) {
@@ -187,7 +219,8 @@ k_seg_long_final(int D4, const int32_t* __restrict__ counters, const int32_t* __
   const int groups = (int)((int64_t)gridDim.x * kThreads / kG);
   const int D = D4 * 4;
   for (int li = (int)(((int64_t)blockIdx.x * kThreads + threadIdx.x) / kG); li < n_long; li += groups) {
-    const int u = long_list[li * 3], base = long_list[li * 3 + 1], nch = long_list[li * 3 + 2];
+    const int u = long_list[li * 4], base = long_list[li * 4 + 1], nch = long_list[li * 4 + 2];
+    if (nch <= 1) continue;   // finished inside k_seg_chunk
     const long long row = epi.row_of(&L, uniq, u);
     float4 p[kC], a0[kC], a1[kC];
     double acc[kC][4];
@@ -197,14 +230,31 @@ k_seg_long_final(int D4, const int32_t* __restrict__ counters, const int32_t* __
       const int col = gl + c * kG;
       if (col < D4) epi.load(row, D4, col, &p[c], &a0[c], &a1[c]);
     }
-    for (int k = 0; k < nch; ++k) {
+    for (int k0 = 0; k0 < nch; k0 += 4) {   // 4 partial rows in flight, added in chunk order
+      double2 x[4][kC], y[4][kC];
 #pragma unroll
-      for (int c = 0; c < kC; ++c) {
-        const int col = gl + c * kG;
-        if (col < D4) {
-          const double2* src = (const double2*)(partial + (size_t)(base + k) * D + col * 4);
-          const double2 x = __ldcg(src), y = __ldcg(src + 1);
-          acc[c][0] += x.x; acc[c][1] += x.y; acc[c][2] += y.x; acc[c][3] += y.y;
+      for (int k = 0; k < 4; ++k) {
+        if (k0 + k < nch) {
+#pragma unroll
+          for (int c = 0; c < kC; ++c) {
+            const int col = gl + c * kG;
+            if (col < D4) {
+              const double2* src = (const double2*)(partial + (size_t)(base + k0 + k) * D + col * 4);
+              x[k][c] = __ldcg(src); y[k][c] = __ldcg(src + 1);
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (k0 + k < nch) {
+#pragma unroll
+          for (int c = 0; c < kC; ++c) {
+            const int col = gl + c * kG;
+            if (col < D4) {
+              acc[c][0] += x[k][c].x; acc[c][1] += x[k][c].y; acc[c][2] += y[k][c].x; acc[c][3] += y[k][c].y;
+            }
+          }
         }
       }
     }
@@ -223,20 +273,24 @@ k_seg_long_final(int D4, const int32_t* __restrict__ counters, const int32_t* __
 
 template <int kG, int kC, typename GT, typename Epi>
 int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t* seg,
-                  const int32_t* n_unique, int64_t max_unique, const int64_t* uniq,
+                  const int32_t* seg_first, const int32_t* n_unique, int64_t max_unique, const int64_t* uniq,
                   const int64_t* layout, Epi epi, const DirectWs& W, cudaStream_t st) {
   const int64_t ctas = edl_cdiv(max_unique * kG, kThreads);
   EDL_REQUIRE(ctas < 0x7fffffff, EDL_ELIMIT, "segreduce: max_unique=%lld too large", (long long)max_unique);
-  k_seg_direct<kG, kC, GT, Epi><<<(unsigned)ctas, kThreads, 0, st>>>(
-      (const unsigned char*)grad, D4, order, seg, n_unique, uniq, layout, epi, W.counters, W.long_list,
+  // 8 CTAs x 256 threads per SM (<= 32 registers) and one row in flight per lane group: measured
+  // faster than fewer, fatter threads (profiles/r1_direct_variants.md) -- the loads that hide HBM
+  // latency come from occupancy, not from unrolling.
+  k_seg_direct<kG, kC, GT, Epi, (kC == 1 ? 8 : 4), 1><<<(unsigned)ctas, kThreads, 0, st>>>(
+      (const unsigned char*)grad, D4, order, seg, seg_first, n_unique, uniq, layout, epi, W.counters, W.long_list,
       W.chunk_list);
-  const int64_t gc = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_chunks * kG, kThreads), EDL_SM_COUNT * 8));
-  k_seg_chunk<kG, kC, GT><<<(unsigned)gc, kThreads, 0, st>>>((const unsigned char*)grad, D4, order, seg,
-                                                             W.counters, W.chunk_list, W.partial);
-  const int64_t gf = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_long * kG, kThreads), EDL_SM_COUNT * 4));
+  const int64_t gc = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_chunks * kG, kThreads), EDL_SM_COUNT * 4));
+  k_seg_chunk<kG, kC, GT, Epi><<<(unsigned)gc, kThreads, 0, st>>>((const unsigned char*)grad, D4, order, seg,
+                                                                  W.counters, W.chunk_list, W.long_list, W.partial,
+                                                                  uniq, layout, epi);
+  const int64_t gf = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_long / 4 * kG, kThreads), EDL_SM_COUNT * 2));
   k_seg_long_final<kG, kC, Epi><<<(unsigned)gf, kThreads, 0, st>>>(D4, W.counters, W.long_list, W.partial, uniq,
                                                                  layout, epi);
-  EDL_LAUNCH_CHECK("k_seg_direct / k_seg_chunk / k_seg_long_final");
+  EDL_LAUNCH_CHECK("k_seg_direct / k_seg_chunk");
   return EDL_OK;
 }
 

@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(kThreads)
 k_unique_write(const KeyT* __restrict__ keys, const uint32_t* __restrict__ order, int64_t n,
                const int32_t* n_dev, const uint32_t* __restrict__ tile_base,
                int64_t* __restrict__ uniq, int32_t* __restrict__ seg_offsets,
-               int32_t* __restrict__ inverse) {
+               int32_t* __restrict__ seg_first, int32_t* __restrict__ inverse) {
   __shared__ unsigned warp_sum[kWarps];
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const int64_t ne = eff_n(n, n_dev);
@@ -308,6 +308,7 @@ k_unique_write(const KeyT* __restrict__ keys, const uint32_t* __restrict__ order
       if (flag[k]) {
         uniq[u] = (int64_t)key[k];
         seg_offsets[u] = (int32_t)i;
+        if (seg_first) seg_first[u] = (int32_t)order[i];
       }
       if (inverse) inverse[order[i]] = (int32_t)u;
     }
@@ -366,8 +367,8 @@ UniqueWs carve_unique(void* ws, int64_t n, int key_bits) {
 template <typename KeyT>
 int unique_impl(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64_t* field_base,
                 int n_fields, int key_bits, int64_t* uniq, int32_t* inverse, int32_t* counts,
-                int32_t* order, int32_t* seg_offsets, int32_t* n_unique, const UniqueWs& W,
-                cudaStream_t st) {
+                int32_t* order, int32_t* seg_offsets, int32_t* seg_first, int32_t* n_unique,
+                const UniqueWs& W, cudaStream_t st) {
   const int tiles = (int)edl_cdiv(n, kTile);
   const int passes = (key_bits + 7) / 8;
   KeyT* kbuf[2] = {(KeyT*)W.keysA, (KeyT*)W.keysB};
@@ -398,7 +399,7 @@ int unique_impl(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64
   k_head_count<KeyT><<<tiles, kThreads, 0, st>>>(sorted, n, n_dev, W.tile_heads);
   k_scan_tiles<<<1, 1024, 0, st>>>(W.tile_heads, tiles, n, n_dev, n_unique, seg_offsets);
   k_unique_write<KeyT><<<tiles, kThreads, 0, st>>>(sorted, (const uint32_t*)order, n, n_dev,
-                                                   W.tile_heads, uniq, seg_offsets, inverse);
+                                                   W.tile_heads, uniq, seg_offsets, seg_first, inverse);
   if (counts) {
     int g = (int)std::min<int64_t>(edl_cdiv(n, 256), EDL_SM_COUNT * 8);
     k_counts<<<g, 256, 0, st>>>(seg_offsets, n_unique, counts);
@@ -417,8 +418,8 @@ extern "C" size_t edl_unique_workspace_bytes(int64_t n, int key_bits) {
 extern "C" int edl_unique(const int64_t* ids, int64_t n, const int32_t* n_dev,
                           const int64_t* field_base, int n_fields, int key_bits, int64_t* uniq,
                           int32_t* inverse, int32_t* counts, int32_t* order, int32_t* seg_offsets,
-                          int32_t* n_unique, void* workspace, size_t workspace_bytes,
-                          edl_stream_t stream) {
+                          int32_t* seg_first, int32_t* n_unique, void* workspace,
+                          size_t workspace_bytes, edl_stream_t stream) {
   cudaStream_t st = (cudaStream_t)stream;
   EDL_REQUIRE(n >= 0 && n < (int64_t)0x7fff0000, EDL_EINVAL, "edl_unique: n=%lld out of range", (long long)n);
   EDL_REQUIRE(key_bits >= 1 && key_bits <= 64, EDL_EINVAL, "edl_unique: key_bits=%d not in 1..64", key_bits);
@@ -436,9 +437,9 @@ extern "C" int edl_unique(const int64_t* ids, int64_t n, const int32_t* n_dev,
               "edl_unique: workspace %zu < required %zu", workspace_bytes, W.bytes);
   if (key_bits <= 32)
     return unique_impl<uint32_t>(ids, n, n_dev, field_base, n_fields, key_bits, uniq, inverse, counts,
-                                 order, seg_offsets, n_unique, W, st);
+                                 order, seg_offsets, seg_first, n_unique, W, st);
   return unique_impl<uint64_t>(ids, n, n_dev, field_base, n_fields, key_bits, uniq, inverse, counts,
-                               order, seg_offsets, n_unique, W, st);
+                               order, seg_offsets, seg_first, n_unique, W, st);
 }
 
 // --------------------------------------------------------------------------------- A2
@@ -533,7 +534,8 @@ int static_scratch(void** out) {
 extern "C" int edl_unique_static(const int64_t* ids, int64_t n, const int32_t* n_dev,
                                  const int64_t* field_base, int n_fields, int key_bits,
                                  int64_t* uniq, int32_t* inverse, int32_t* counts, int32_t* order,
-                                 int32_t* seg_offsets, int32_t* n_unique, edl_stream_t stream) {
+                                 int32_t* seg_offsets, int32_t* seg_first, int32_t* n_unique,
+                                 edl_stream_t stream) {
   cudaStream_t st = (cudaStream_t)stream;
   EDL_REQUIRE(n >= 0, EDL_EINVAL, "edl_unique_static: n=%lld negative", (long long)n);
   EDL_REQUIRE(n <= (int64_t)EDL_UNIQUE_STATIC_MAX_IDS, EDL_ELIMIT,
@@ -561,7 +563,7 @@ extern "C" int edl_unique_static(const int64_t* ids, int64_t n, const int32_t* n
   // left behind is never observed.
   if (key_bits <= 32)
     return unique_impl<uint32_t>(ids, n, n_dev, field_base, n_fields, key_bits, uniq, inverse, counts,
-                                 order, seg_offsets, n_unique, W, st);
+                                 order, seg_offsets, seg_first, n_unique, W, st);
   return unique_impl<uint64_t>(ids, n, n_dev, field_base, n_fields, key_bits, uniq, inverse, counts,
-                               order, seg_offsets, n_unique, W, st);
+                               order, seg_offsets, seg_first, n_unique, W, st);
 }

@@ -31,7 +31,7 @@ Ws carve_ws(void* ws, int64_t n_rows, int dim) {
   const int64_t n = n_rows > 0 ? n_rows : 0;
   w.direct.max_long = n / (kLongThr + 1) + 1;
   w.direct.max_chunks = n / kChunk + w.direct.max_long + 1;
-  w.direct.long_list = (int32_t*)(p + off); off = edl_align_up(off + (size_t)w.direct.max_long * 3 * 4, 256);
+  w.direct.long_list = (int32_t*)(p + off); off = edl_align_up(off + (size_t)w.direct.max_long * 4 * 4, 256);
   w.direct.chunk_list = (int32_t*)(p + off); off = edl_align_up(off + (size_t)w.direct.max_chunks * 2 * 4, 256);
   w.direct.partial = (double*)(p + off); off = edl_align_up(off + (size_t)w.direct.max_chunks * dim * 8, 256);
   w.tile.bytes = off;
@@ -50,14 +50,14 @@ bool use_tile_impl() {
 
 template <typename GT, typename Epi>
 int dispatch_dim(const void* grad, int dim, const int32_t* order, const int32_t* seg,
-                 const int32_t* n_unique, int64_t max_unique, const int64_t* uniq,
+                 const int32_t* seg_first, const int32_t* n_unique, int64_t max_unique, const int64_t* uniq,
                  const int64_t* layout, Epi epi, const Ws& W, cudaStream_t st) {
   const int D4 = dim / 4;
   EDL_CUDA(cudaMemsetAsync(W.tile.flags, 0, W.zero_bytes, st));
   const bool tile = use_tile_impl();
 #define EDL_GO(G, C)                                                                                          \
   return tile ? launch_tile<G, C, GT, Epi>(grad, D4, order, seg, n_unique, max_unique, uniq, layout, epi, W.tile, st) \
-              : launch_direct<G, C, GT, Epi>(grad, D4, order, seg, n_unique, max_unique, uniq, layout, epi, W.direct, st)
+              : launch_direct<G, C, GT, Epi>(grad, D4, order, seg, seg_first, n_unique, max_unique, uniq, layout, epi, W.direct, st)
   if (D4 <= 4) EDL_GO(4, 1);
   if (D4 <= 8) EDL_GO(8, 1);
   if (D4 <= 16) EDL_GO(16, 1);
@@ -91,7 +91,8 @@ extern "C" size_t edl_segreduce_workspace_bytes(int64_t max_unique, int64_t n_ro
 }
 
 extern "C" int edl_segreduce(const float* grad, int dim, const int32_t* order,
-                             const int32_t* seg_offsets, const int32_t* n_unique_dev,
+                             const int32_t* seg_offsets, const int32_t* seg_first,
+                             const int32_t* n_unique_dev,
                              int64_t max_unique, int64_t n_rows, const int32_t* out_pos, void* g_out, int out_f64,
                              void* workspace, size_t workspace_bytes, edl_stream_t stream) {
   if (max_unique == 0) return EDL_OK;
@@ -103,17 +104,18 @@ extern "C" int edl_segreduce(const float* grad, int dim, const int32_t* order,
   cudaStream_t st = (cudaStream_t)stream;
   if (out_f64) {
     EpiWrite64 epi{(double*)g_out, out_pos};
-    return dispatch_dim<float, EpiWrite64>(grad, dim, order, seg_offsets, n_unique_dev, max_unique, nullptr,
+    return dispatch_dim<float, EpiWrite64>(grad, dim, order, seg_offsets, seg_first, n_unique_dev, max_unique, nullptr,
                                            nullptr, epi, W, st);
   }
   EpiWrite epi{(float4*)g_out, out_pos};
-  return dispatch_dim<float, EpiWrite>(grad, dim, order, seg_offsets, n_unique_dev, max_unique, nullptr,
+  return dispatch_dim<float, EpiWrite>(grad, dim, order, seg_offsets, seg_first, n_unique_dev, max_unique, nullptr,
                                        nullptr, epi, W, st);
 }
 
 extern "C" int edl_segreduce_update(float* slab, float* slot0, float* slot1, int dim,
                                     const int64_t* uniq, const int32_t* order,
-                                    const int32_t* seg_offsets, const int32_t* n_unique_dev,
+                                    const int32_t* seg_offsets, const int32_t* seg_first,
+                                    const int32_t* n_unique_dev,
                                     int64_t max_unique, int64_t n_rows, const void* grad, int grad_f64,
                                     const int64_t* layout, const edl_opt_params* opt,
                                     uint32_t* touched, void* workspace, size_t workspace_bytes,
@@ -134,14 +136,14 @@ extern "C" int edl_segreduce_update(float* slab, float* slot0, float* slot1, int
   cudaStream_t st = (cudaStream_t)stream;
   if (opt->kind == EDL_OPT_ADAGRAD) {
     EpiAdagrad epi{(float4*)slab, (float4*)slot0, touched, o};
-    return grad_f64 ? dispatch_dim<double, EpiAdagrad>(grad, dim, order, seg_offsets, n_unique_dev, max_unique, uniq, layout, epi, W, st)
-                    : dispatch_dim<float, EpiAdagrad>(grad, dim, order, seg_offsets, n_unique_dev, max_unique, uniq, layout, epi, W, st);
+    return grad_f64 ? dispatch_dim<double, EpiAdagrad>(grad, dim, order, seg_offsets, seg_first, n_unique_dev, max_unique, uniq, layout, epi, W, st)
+                    : dispatch_dim<float, EpiAdagrad>(grad, dim, order, seg_offsets, seg_first, n_unique_dev, max_unique, uniq, layout, epi, W, st);
   }
   if (opt->kind == EDL_OPT_ADAM) {
     EDL_REQUIRE(slot1, EDL_EINVAL, "edl_segreduce_update: Adam needs slot1 (v)");
     EpiAdam epi{(float4*)slab, (float4*)slot0, (float4*)slot1, touched, o};
-    return grad_f64 ? dispatch_dim<double, EpiAdam>(grad, dim, order, seg_offsets, n_unique_dev, max_unique, uniq, layout, epi, W, st)
-                    : dispatch_dim<float, EpiAdam>(grad, dim, order, seg_offsets, n_unique_dev, max_unique, uniq, layout, epi, W, st);
+    return grad_f64 ? dispatch_dim<double, EpiAdam>(grad, dim, order, seg_offsets, seg_first, n_unique_dev, max_unique, uniq, layout, epi, W, st)
+                    : dispatch_dim<float, EpiAdam>(grad, dim, order, seg_offsets, seg_first, n_unique_dev, max_unique, uniq, layout, epi, W, st);
   }
   edl_set_error("edl_segreduce_update: unknown optimizer kind %d", opt->kind);
   return EDL_EINVAL;

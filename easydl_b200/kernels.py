@@ -72,6 +72,7 @@ class UniqueResult:
     seg_offsets: torch.Tensor   # int32 [n+1]
     n_unique: torch.Tensor      # int32 [1] on device
     n: int
+    seg_first: Optional[torch.Tensor] = None  # int32 [n]: order[seg_offsets[u]]
 
     def count(self) -> int:
         """Host value of U (synchronises)."""
@@ -102,14 +103,15 @@ def unique(ids: torch.Tensor, field_base: Optional[torch.Tensor] = None, key_bit
             counts=torch.empty(n, dtype=torch.int32, device=dev) if want_counts else None,
             order=torch.empty(n, dtype=torch.int32, device=dev),
             seg_offsets=torch.empty(n + 1, dtype=torch.int32, device=dev),
-            n_unique=torch.empty(1, dtype=torch.int32, device=dev), n=n)
+            n_unique=torch.empty(1, dtype=torch.int32, device=dev), n=n,
+            seg_first=torch.empty(max(n, 1), dtype=torch.int32, device=dev))
     need = lib.edl_unique_workspace_bytes(n, key_bits)
     if workspace is None or workspace.numel() < need:
         workspace = _ws(need, dev)
     check(lib.edl_unique(_ptr(ids), n, _ptr(n_dev), _ptr(field_base), n_fields, key_bits,
                          _ptr(out.uniq), _ptr(out.inverse), _ptr(out.counts), _ptr(out.order),
-                         _ptr(out.seg_offsets), _ptr(out.n_unique), _ptr(workspace),
-                         workspace.numel(), _stream()), "edl_unique")
+                         _ptr(out.seg_offsets), _ptr(out.seg_first), _ptr(out.n_unique),
+                         _ptr(workspace), workspace.numel(), _stream()), "edl_unique")
     return out
 
 
@@ -204,7 +206,8 @@ def scatter_rows(rows: torch.Tensor, pos: torch.Tensor, out: torch.Tensor, *,
 
 # ------------------------------------------------------------------------------- A4 / A5
 def segreduce(grad: torch.Tensor, order: torch.Tensor, seg_offsets: torch.Tensor,
-              n_unique: torch.Tensor, max_unique: int, *, out_pos: Optional[torch.Tensor] = None,
+              n_unique: torch.Tensor, max_unique: int, *, seg_first: Optional[torch.Tensor] = None,
+              out_pos: Optional[torch.Tensor] = None,
               out: Optional[torch.Tensor] = None, out_dtype=torch.float32,
               workspace: Optional[torch.Tensor] = None):
     """g[dst(u)] = float64 segment sum; out_dtype float32 (rounded once) or float64 (exact wire)."""
@@ -221,8 +224,8 @@ def segreduce(grad: torch.Tensor, order: torch.Tensor, seg_offsets: torch.Tensor
     need = lib.edl_segreduce_workspace_bytes(max_unique, n_rows, dim)
     if workspace is None or workspace.numel() < need:
         workspace = _ws(need, grad.device)
-    check(lib.edl_segreduce(_ptr(grad), dim, _ptr(order), _ptr(seg_offsets), _ptr(n_unique),
-                            max_unique, n_rows, _ptr(out_pos), _ptr(out), int(out.dtype == torch.float64),
+    check(lib.edl_segreduce(_ptr(grad), dim, _ptr(order), _ptr(seg_offsets), _ptr(seg_first),
+                            _ptr(n_unique), max_unique, n_rows, _ptr(out_pos), _ptr(out), int(out.dtype == torch.float64),
                             _ptr(workspace), workspace.numel(), _stream()), "edl_segreduce")
     return out
 
@@ -232,7 +235,8 @@ def segreduce_update(slab: torch.Tensor, slot0: torch.Tensor, slot1: Optional[to
                      n_unique: torch.Tensor, max_unique: int, grad: torch.Tensor,
                      layout: Optional[torch.Tensor], opt: OptParams,
                      touched: Optional[torch.Tensor] = None,
-                     workspace: Optional[torch.Tensor] = None):
+                     workspace: Optional[torch.Tensor] = None,
+                     seg_first: Optional[torch.Tensor] = None):
     """grad rows may be float32 (a worker's raw gradient) or float64 (exchanged partial sums)."""
     lib = _lib.load()
     _need(slab, torch.float32, "slab")
@@ -249,8 +253,8 @@ def segreduce_update(slab: torch.Tensor, slot0: torch.Tensor, slot1: Optional[to
     if workspace is None or workspace.numel() < need:
         workspace = _ws(need, slab.device)
     check(lib.edl_segreduce_update(_ptr(slab), _ptr(slot0), _ptr(slot1), dim, _ptr(uniq),
-                                   _ptr(order), _ptr(seg_offsets), _ptr(n_unique), max_unique,
-                                   n_rows, _ptr(grad), int(grad.dtype == torch.float64), _ptr(layout),
+                                   _ptr(order), _ptr(seg_offsets), _ptr(seg_first), _ptr(n_unique),
+                                   max_unique, n_rows, _ptr(grad), int(grad.dtype == torch.float64), _ptr(layout),
                                    C.byref(opt), _ptr(touched), _ptr(workspace), workspace.numel(),
                                    _stream()), "edl_segreduce_update")
 

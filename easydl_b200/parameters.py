@@ -94,7 +94,8 @@ class ShardParameters:
         slot1 = self.slots[1] if len(self.slots) > 1 else None
         K.segreduce_update(self.slab, self.slots[0], slot1, uq.uniq, uq.order, uq.seg_offsets,
                            uq.n_unique, uq.n if max_unique is None else max_unique, grad,
-                           self._layout_arg, self.opt.params(self.step), self.touched, workspace)
+                           self._layout_arg, self.opt.params(self.step), self.touched, workspace,
+                           seg_first=uq.seg_first)
 
     # ------------------------------------------------------------------ A6
     def export_records(self) -> ShardRecords:

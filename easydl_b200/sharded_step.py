@@ -69,7 +69,8 @@ class ShardedSparseStep:
     def gen_update(self, grad: torch.Tensor) -> Generator:
         uq, part, send, recv, recv_keys, U = self._fw
         g_send = torch.empty((max(U, 1), self.params.dim), dtype=self.wire_dtype, device=grad.device)
-        K.segreduce(grad, uq.order, uq.seg_offsets, uq.n_unique, uq.n, out_pos=part.pos, out=g_send)
+        K.segreduce(grad, uq.order, uq.seg_offsets, uq.n_unique, uq.n, seg_first=uq.seg_first,
+                    out_pos=part.pos, out=g_send)
         g_recv = yield ("a2av", g_send[:U], send, recv)      # aligned with recv_keys
         R = recv_keys.numel()
         if R == 0:

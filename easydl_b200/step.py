@@ -35,7 +35,8 @@ class SparseStep:
             uniq=torch.empty(N, dtype=torch.int64, device=dev), inverse=None, counts=None,
             order=torch.empty(N, dtype=torch.int32, device=dev),
             seg_offsets=torch.empty(N + 1, dtype=torch.int32, device=dev),
-            n_unique=torch.zeros(1, dtype=torch.int32, device=dev), n=N)
+            n_unique=torch.zeros(1, dtype=torch.int32, device=dev), n=N,
+            seg_first=torch.empty(N, dtype=torch.int32, device=dev))
         self.ws_unique = torch.empty(lib.edl_unique_workspace_bytes(N, self.key_bits),
                                      dtype=torch.uint8, device=dev)
         self.ws_seg = torch.empty(lib.edl_segreduce_workspace_bytes(N, N, D), dtype=torch.uint8, device=dev)

@@ -68,6 +68,8 @@ int edl_fill_f32(float* dst, int64_t n, float value, edl_stream_t stream);
  * Outputs (each nullable except uniq, order, seg_offsets, n_unique):
  *   uniq[U] ascending int64, inverse[n] int32, counts[U] int32,
  *   order[n] int32 = stable argsort(keys), seg_offsets[U+1] int32 (seg_offsets[U] = n),
+ *   seg_first[U] int32 (nullable) = order[seg_offsets[u]], the first batch position of each
+ *   id: lets the reduce kernels skip one dependent load for ids that occur once,
  *   n_unique: device int32 scalar U.
  * Only the low key_bits bits of the keys may be non-zero (1..64).
  * n_dev (nullable): device int32 holding the actual n (<= n); used when the input length
@@ -75,8 +77,8 @@ int edl_fill_f32(float* dst, int64_t n, float value, edl_stream_t stream);
 size_t edl_unique_workspace_bytes(int64_t n, int key_bits);
 int edl_unique(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64_t* field_base,
                int n_fields, int key_bits, int64_t* uniq, int32_t* inverse, int32_t* counts,
-               int32_t* order, int32_t* seg_offsets, int32_t* n_unique, void* workspace,
-               size_t workspace_bytes, edl_stream_t stream);
+               int32_t* order, int32_t* seg_offsets, int32_t* seg_first, int32_t* n_unique,
+               void* workspace, size_t workspace_bytes, edl_stream_t stream);
 
 /* ---- A1 for callers that cannot allocate device memory -----------------------------------
  * No counterpart in the reference (nor in the ElasticDL lineage): added for this library's
@@ -106,7 +108,8 @@ int edl_unique(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64_
 #define EDL_UNIQUE_STATIC_SCRATCH_BYTES (3 * 1024 * 1024)
 int edl_unique_static(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64_t* field_base,
                       int n_fields, int key_bits, int64_t* uniq, int32_t* inverse, int32_t* counts,
-                      int32_t* order, int32_t* seg_offsets, int32_t* n_unique, edl_stream_t stream);
+                      int32_t* order, int32_t* seg_offsets, int32_t* seg_first, int32_t* n_unique,
+                      edl_stream_t stream);
 
 /* ---- A2 hash-mod partition (lineage int_to_id / scatter_embedding_vector) --------------
  * Stable partition of keys[0..n) by (per-table id mod S'), S' = num_shards (1..256), tables
@@ -145,7 +148,7 @@ int edl_compose_index(const int32_t* index, const int32_t* map, int64_t n, int32
  * rows (= length of `order`), which bounds the scratch for hot ids. */
 size_t edl_segreduce_workspace_bytes(int64_t max_unique, int64_t n_rows, int dim);
 int edl_segreduce(const float* grad, int dim, const int32_t* order, const int32_t* seg_offsets,
-                  const int32_t* n_unique_dev, int64_t max_unique, int64_t n_rows,
+                  const int32_t* seg_first /* nullable */, const int32_t* n_unique_dev, int64_t max_unique, int64_t n_rows,
                   const int32_t* out_pos, void* g_out, int out_f64, void* workspace,
                   size_t workspace_bytes, edl_stream_t stream);
 
@@ -168,7 +171,8 @@ typedef struct edl_opt_params {
 
 int edl_segreduce_update(float* slab, float* slot0, float* slot1, int dim, const int64_t* uniq,
                          const int32_t* order, const int32_t* seg_offsets,
-                         const int32_t* n_unique_dev, int64_t max_unique, int64_t n_rows,
+                         const int32_t* seg_first /* nullable */, const int32_t* n_unique_dev,
+                         int64_t max_unique, int64_t n_rows,
                          const void* grad, int grad_f64, const int64_t* layout, const edl_opt_params* opt_host,
                          uint32_t* touched, void* workspace, size_t workspace_bytes,
                          edl_stream_t stream);

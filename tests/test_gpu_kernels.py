@@ -60,6 +60,7 @@ def _check_unique(cuda, keys_np, field_base=None, key_bits=64, ids_np=None):
     assert np.array_equal(r.counts[:U].cpu().numpy(), cnt)
     assert np.array_equal(r.order.cpu().numpy(), order)
     assert np.array_equal(r.seg_offsets[:U + 1].cpu().numpy(), seg)
+    assert np.array_equal(r.seg_first[:U].cpu().numpy(), order[seg[:-1]])
 
 
 @pytest.mark.parametrize("n,hi,bits", [(1, 10, 8), (2, 2, 1), (31, 5, 3), (2048, 300, 9), (2049, 1 << 20, 20),

@@ -31,6 +31,7 @@ def _call_static(lib, ids, field_base, key_bits):
         counts=torch.full((max(n, 1),), -1, dtype=torch.int32, device=dev),
         order=torch.full((max(n, 1),), -1, dtype=torch.int32, device=dev),
         seg=torch.full((n + 1,), -1, dtype=torch.int32, device=dev),
+        first=torch.full((max(n, 1),), -1, dtype=torch.int32, device=dev),
         nu=torch.full((1,), -1, dtype=torch.int32, device=dev),
     )
     fb_ptr = None if field_base is None else field_base.data_ptr()
@@ -38,7 +39,7 @@ def _call_static(lib, ids, field_base, key_bits):
     rc = lib.edl_unique_static(
         ids.data_ptr() if n else None, n, None, fb_ptr, nf, key_bits,
         out["uniq"].data_ptr(), out["inverse"].data_ptr(), out["counts"].data_ptr(),
-        out["order"].data_ptr(), out["seg"].data_ptr(), out["nu"].data_ptr(),
+        out["order"].data_ptr(), out["seg"].data_ptr(), out["first"].data_ptr(), out["nu"].data_ptr(),
         torch.cuda.current_stream().cuda_stream)
     return rc, out
 
@@ -51,6 +52,7 @@ def _compare(out, ref, n):
     assert torch.equal(out["counts"][:U], ref.counts[:U])
     assert torch.equal(out["order"][:n], ref.order[:n])
     assert torch.equal(out["seg"][:U + 1], ref.seg_offsets[:U + 1])
+    assert torch.equal(out["first"][:U], ref.seg_first[:U])
 
 
 def test_static_scratch_unique_matches_edl_unique_twice(cuda):

@@ -1,0 +1,5 @@
+# timing of k_seg_direct launch-bound / unroll variants at the cfg2 shape
+B="python bench.py --steps 50 --warmup 5 --no-cpu-baseline --no-e2e"
+for v in ${VARIANTS:-0 1 2 3 4 5}; do
+  echo "variant=$v: $(EDL_DIRECT_VARIANT=$v timeout 200 $B 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('update_ms', round(d['phases']['update_ms'],4), 'step_ms', round(d['ms_per_step'],4))")"
+done
