@@ -14,7 +14,7 @@
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kUnroll = 4;
+constexpr int kUnroll = 2;
 
 // ------------------------------------------------------------------ row init
 __device__ __forceinline__ unsigned long long splitmix64(unsigned long long x) {
@@ -90,7 +90,7 @@ struct IndexRowFn {  // int32 index (expand by `inverse`, permute by `perm`)
 
 // kD4 > 0: compile-time row width in float4 (power of two); kD4 == 0: runtime width.
 template <int kD4, typename RowFn, bool kUseLayout>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 8)
 k_gather(const float4* __restrict__ src, int D4_rt, RowFn fn, int64_t n, const int32_t* n_dev,
          const int64_t* __restrict__ layout, float4* __restrict__ out) {
   __shared__ EdlLayoutSmem L;
