@@ -8,6 +8,11 @@ backward: A4 reduce grad by local unique id, written in partition order -> [grad
           peer-rank order) -> A4 reduce -> A5 optimizer in place.
 
 One host synchronisation per step: the split sizes of the all-to-all-v (counts round).
+
+The choreography (what is sent to whom, in which order, with which split sizes) is written
+against a small `ops` interface.  The product binds it to the CUDA kernels (CudaOps, no
+fallback); the world-size-2 gloo tests bind the same choreography to a test double so that
+the exchange bookkeeping is exercised on CPU tensors without a GPU.
 """
 from __future__ import annotations
 
@@ -19,65 +24,90 @@ from . import kernels as K
 from .parameters import ShardParameters
 
 
+class CudaOps:
+    """The step's compute, bound to libedlsparse on one shard's device state."""
+
+    def __init__(self, params: ShardParameters, n_fields: int):
+        self.params = params
+        dev = params.device
+        self.field_base = torch.from_numpy(params.layout.key_base[:n_fields].copy()).to(dev)
+        self.key_bits = params.layout.key_bits
+        self.layout_dev = params.layout_dev          # T and key_base are what partition reads
+        self.dim = params.dim
+
+    def unique(self, flat_ids):
+        return K.unique(flat_ids, self.field_base, self.key_bits, want_inverse=True, want_counts=False)
+
+    def partition(self, uq, num_shards: int):
+        return K.partition_mod(uq.uniq, self.layout_dev, num_shards, n_dev=uq.n_unique)
+
+    def lookup(self, keys):
+        return self.params.lookup(keys)
+
+    def expand(self, rows_in, uq, part):
+        return K.expand(rows_in, K.compose_index(uq.inverse, part.pos))
+
+    def reduce_for_send(self, grad, uq, part, n_send: int, wire_dtype):
+        g_send = torch.empty((max(n_send, 1), self.dim), dtype=wire_dtype, device=grad.device)
+        K.segreduce(grad, uq.order, uq.seg_offsets, uq.n_unique, uq.n, seg_first=uq.seg_first,
+                    out_pos=part.pos, out=g_send)
+        return g_send[:n_send]
+
+    def apply(self, recv_keys, g_recv):
+        R = recv_keys.numel()
+        if R == 0:
+            self.params.step += 1
+            return
+        uq2 = K.unique(recv_keys, None, self.key_bits, want_inverse=False, want_counts=False)
+        self.params.apply_gradients(uq2, g_recv, R)
+
+
 class ShardedSparseStep:
-    def __init__(self, params: ShardParameters, batch_size: int, exchange=None,
-                 n_fields: Optional[int] = None, wire_dtype=torch.float64):
+    def __init__(self, params: Optional[ShardParameters], batch_size: int, exchange=None,
+                 n_fields: Optional[int] = None, wire_dtype=torch.float64, *, num_shards=None,
+                 _ops=None):
         # wire_dtype: element type of the per-worker partial gradient sums on the wire.
         # float64 (default) keeps the owner's total equal to one float64 pass over the global
         # batch (SPEC A4: independent of S and of the worker split); float32 halves the
         # gradient exchange bytes at the cost of one extra fp32 rounding per worker.
         self.wire_dtype = wire_dtype
         self.params = params
-        self.S = params.num_shards
-        self.rank = params.shard
+        self.S = params.num_shards if params is not None else int(num_shards)
         self.exchange = exchange
-        self.F = params.layout.n_tables if n_fields is None else n_fields
+        self.F = (params.layout.n_tables if n_fields is None else n_fields) if params is not None else n_fields
         self.B = int(batch_size)
         self.N = self.B * self.F
-        dev = params.device
-        self.field_base = torch.from_numpy(params.layout.key_base[:self.F].copy()).to(dev)
-        self.key_bits = params.layout.key_bits
-        self.layout_dev = params.layout_dev          # T and key_base are what partition reads
-        self.last_n_unique = torch.zeros(1, dtype=torch.int32, device=dev)
-        passes = (self.key_bits + 7) // 8
-        # unique x2, partition 4, gather 1, compose 1, expand 1, segreduce 3, update 3
-        self.launches_per_step = 2 * (3 * passes + 4) + 4 + 1 + 1 + 1 + 3 + 3
+        self.ops = _ops if _ops is not None else CudaOps(params, self.F)
+        self.last_n_unique = None
+        if params is not None:
+            passes = (params.layout.key_bits + 7) // 8
+            # unique x2, partition 4, gather 1, compose 1, expand 1, segreduce 4, update 4
+            self.launches_per_step = 2 * (3 * passes + 3) + 4 + 1 + 1 + 1 + 4 + 4
         self._fw = None
 
     # ------------------------------------------------------------------ generators
     def gen_lookup(self, ids: torch.Tensor) -> Generator:
         S = self.S
-        flat = ids.reshape(-1)
-        uq = K.unique(flat, self.field_base, self.key_bits, want_inverse=True, want_counts=False)
-        part = K.partition_mod(uq.uniq, self.layout_dev, S, n_dev=uq.n_unique)
+        uq = self.ops.unique(ids.reshape(-1))
+        part = self.ops.partition(uq, S)
         counts = (part.offsets[1:] - part.offsets[:-1]).to(torch.int64).reshape(S, 1)
         got = yield ("counts", counts)                       # host [S, 1]: what each peer sends us
-        send = [int(x) for x in counts.cpu().reshape(-1)] if S == 1 else None
-        if send is None:
-            send = [int(x) for x in part.offsets.cpu().diff()]
+        send = [int(x) for x in counts.cpu().reshape(-1)]
         recv = [int(x) for x in got.reshape(-1)]
         U = sum(send)
         recv_keys = yield ("a2av", part.keys[:U], send, recv)
-        rows_out = self.params.lookup(recv_keys)
+        rows_out = self.ops.lookup(recv_keys)
         rows_in = yield ("a2av", rows_out, recv, send)       # [U, D], partition order
-        index = K.compose_index(uq.inverse, part.pos)
-        emb = K.expand(rows_in, index)
+        emb = self.ops.expand(rows_in, uq, part)
         self._fw = (uq, part, send, recv, recv_keys, U)
         self.last_n_unique = uq.n_unique
         return emb
 
     def gen_update(self, grad: torch.Tensor) -> Generator:
         uq, part, send, recv, recv_keys, U = self._fw
-        g_send = torch.empty((max(U, 1), self.params.dim), dtype=self.wire_dtype, device=grad.device)
-        K.segreduce(grad, uq.order, uq.seg_offsets, uq.n_unique, uq.n, seg_first=uq.seg_first,
-                    out_pos=part.pos, out=g_send)
-        g_recv = yield ("a2av", g_send[:U], send, recv)      # aligned with recv_keys
-        R = recv_keys.numel()
-        if R == 0:
-            self.params.step += 1
-            return None
-        uq2 = K.unique(recv_keys, None, self.key_bits, want_inverse=False, want_counts=False)
-        self.params.apply_gradients(uq2, g_recv, R)
+        g_send = self.ops.reduce_for_send(grad, uq, part, U, self.wire_dtype)
+        g_recv = yield ("a2av", g_send, send, recv)          # aligned with recv_keys
+        self.ops.apply(recv_keys, g_recv)
         return None
 
     def gen_step(self, ids: torch.Tensor, grad: torch.Tensor) -> Generator:
