@@ -52,6 +52,10 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
+    ap.add_argument("--force-sharded", action="store_true",
+                    help="N=1 only: run the multi-shard code path (dedup/partition/exchange/expand) with S=1")
+    ap.add_argument("--wire", default="f64", choices=["f64", "f32"],
+                    help="element type of exchanged partial gradient sums (N>1)")
     return ap.parse_args()
 
 
@@ -209,13 +213,15 @@ def run_b200_arm(a):
     N = B * F
     params = ShardParameters(rows, D, opt, world, rank, device=dev)
 
-    if world == 1:
+    sharded = world > 1 or a.force_sharded
+    if not sharded:
         from easydl_b200.step import SparseStep
         step = SparseStep(params, B)
     else:
         from easydl_b200.sharded_step import ShardedSparseStep
-        from easydl_b200.exchange import TorchExchange
-        step = ShardedSparseStep(params, B, TorchExchange(dist.group.WORLD, dev))
+        from easydl_b200.exchange import SingleExchange, TorchExchange
+        ex = TorchExchange(dist.group.WORLD, dev) if world > 1 else SingleExchange()
+        step = ShardedSparseStep(params, B, ex, wire_dtype=torch.float64 if a.wire == "f64" else torch.float32)
 
     # distinct batches per rank: step index = batch_no * world + rank
     src = CriteoSynthetic(rows, B, a.alpha)
@@ -237,7 +243,7 @@ def run_b200_arm(a):
     # S == 1, Adagrad: the step is replayed from CUDA graphs (one per id batch buffer), which
     # removes the host launch gaps between its 17 kernels.  Otherwise: eager launches.
     graphed = None
-    if world == 1 and a.optimizer == "adagrad" and not a.no_graph:
+    if not sharded and a.optimizer == "adagrad" and not a.no_graph:
         from easydl_b200.step import GraphedStep
         graphed = [GraphedStep(step, ids_dev[i], grad_dev) for i in range(nb)]
 
@@ -250,7 +256,7 @@ def run_b200_arm(a):
     # unique ids per batch (deterministic per batch buffer): read once, outside the timed region
     U_batch = []
     for i in range(nb):
-        if world == 1:
+        if not sharded:
             U_batch.append(int(step.dedup(ids_dev[i]).n_unique.item()))
         else:
             step.run(ids_dev[i], grad_dev)
@@ -279,7 +285,7 @@ def run_b200_arm(a):
 
     # ---------------- per-phase timing (same K steps again, events between the phases)
     phases = None
-    if world == 1:
+    if not sharded:
         ev = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(a.steps)]
         if sampler:
             sampler.active = True
@@ -353,6 +359,8 @@ def run_b200_arm(a):
             "config": {"workload": workload_name(a), "global_batch": B * world,
                        "tables": F, "rows_per_table": a.rows, "dim": D, "zipf_alpha": a.alpha,
                        "unique_per_step": U_mean, "sharding": f"row-wise id mod {world}",
+                       "code_path": "sharded" if sharded else "single-shard fused",
+                       "gradient_wire": a.wire if sharded else None,
                        "cache": "inputs larger than L2: 133 GB of table rows touched at random, "
                                 f"{nb} id batches cycled, 436 MB gradient + 436 MB output per step"},
             "gpu_launches": step.launches_per_step * a.steps,
