@@ -31,3 +31,96 @@ class HostStepRunner:
         st.update(self.ids_dev, self.grad_dev)
         self.nu_host.copy_(st.last_n_unique, non_blocking=True)
         return self.emb_host
+
+
+class PSClient:
+    """Worker-side view of S parameter-server shards living in this process (one per GPU, or
+    several virtual shards on one GPU).  Lineage surface: `pull_embedding_vectors(name, ids)`
+    and `push_gradients(...)` take and return HOST arrays, exactly what a worker <-> PS RPC
+    would carry; the fused forms take a whole [B, F] id batch.
+
+    Per call: ids H2D -> A1 dedup -> A2 partition by owner -> per-shard A3 gather ->
+    reassemble -> expand -> D2H."""
+
+    def __init__(self, servers):
+        from .hash_utils import scatter_embedding_vector
+        self._scatter = scatter_embedding_vector
+        self.servers = list(servers)
+        self.S = len(self.servers)
+        p0 = self.servers[0].embedding_params
+        self.layout = p0.layout
+        self.device = p0.device
+        self.key_bits = p0.layout.key_bits
+        self.layout_dev = p0.layout_dev
+        self.field_base = torch.from_numpy(p0.layout.key_base[:-1].copy()).to(self.device)
+        self._last = None
+
+    # ---- helpers
+    def _pull_keys(self, flat_ids_dev, field_base):
+        from . import kernels as K
+        uq = K.unique(flat_ids_dev, field_base, self.key_bits, want_inverse=True, want_counts=False)
+        U = uq.count()
+        keys_by, offs, _, perm = self._scatter(None, uq.uniq[:U], self.S, self.layout_dev)
+        rows = torch.empty((max(U, 1), self.servers[0].embedding_params.dim), dtype=torch.float32,
+                           device=self.device)
+        for s, ps in enumerate(self.servers):
+            a, b = offs[s], offs[s + 1]
+            if b > a:
+                dev_s = ps.embedding_params.device
+                r = ps.pull_embedding_keys(keys_by[a:b].to(dev_s))
+                rows[a:b] = r.to(self.device)
+        pos = torch.empty(max(U, 1), dtype=torch.int32, device=self.device)
+        pos[perm[:U].long()] = torch.arange(U, dtype=torch.int32, device=self.device)
+        emb = K.expand(rows, K.compose_index(uq.inverse, pos))
+        return emb, (uq, U, keys_by, offs, pos)
+
+    # ---- lineage calls (host arrays)
+    def pull_embedding_vectors(self, layer_name: str, ids):
+        """ids: 1-D host array of per-table ids (duplicates allowed) -> [n, dim] host array."""
+        t = self.servers[0].names.index(layer_name)
+        d = torch.as_tensor(ids, dtype=torch.int64).reshape(-1).to(self.device)
+        fb = self.field_base[t:t + 1].contiguous()
+        emb, _ = self._pull_keys(d, fb)
+        return emb.cpu().numpy()
+
+    def pull_embedding_batch(self, ids):
+        """ids: host [B, F] (field f reads table f) -> host [B, F, dim]; remembers the dedup for
+        the matching push_gradient_batch."""
+        ids_t = torch.as_tensor(ids, dtype=torch.int64)
+        B, F = ids_t.shape
+        emb, st = self._pull_keys(ids_t.to(self.device).reshape(-1), self.field_base[:F].contiguous())
+        self._last = st
+        return emb.cpu().numpy().reshape(B, F, -1)
+
+    def push_gradient_batch(self, grads):
+        """grads: host [B, F, dim], gradient of the last pull_embedding_batch's output."""
+        from . import kernels as K
+        uq, U, keys_by, offs, pos = self._last
+        g = torch.as_tensor(grads, dtype=torch.float32).reshape(uq.n, -1).to(self.device)
+        g_send = torch.empty((max(U, 1), g.shape[1]), dtype=torch.float64, device=self.device)
+        K.segreduce(g, uq.order, uq.seg_offsets, uq.n_unique, uq.n, seg_first=uq.seg_first,
+                    out_pos=pos, out=g_send)
+        for s, ps in enumerate(self.servers):
+            a, b = offs[s], offs[s + 1]
+            dev_s = ps.embedding_params.device
+            ps.push_gradients(keys_by[a:b].to(dev_s), g_send[a:b].to(dev_s))
+
+    def push_gradients(self, layer_name: str, ids, grads):
+        """(ids, grads) of one table as host arrays, duplicates allowed (an IndexedSlices)."""
+        from . import kernels as K
+        t = self.servers[0].names.index(layer_name)
+        keys = torch.as_tensor(ids, dtype=torch.int64).reshape(-1).to(self.device) + int(self.layout.key_base[t])
+        g = torch.as_tensor(grads, dtype=torch.float32).to(self.device).contiguous()
+        keys_by, offs, rows_by, _ = self._scatter(g, keys, self.S, self.layout_dev)
+        for s, ps in enumerate(self.servers):
+            a, b = offs[s], offs[s + 1]
+            dev_s = ps.embedding_params.device
+            ps.push_gradients(keys_by[a:b].to(dev_s).contiguous(),
+                              (rows_by[a:b] if rows_by is not None else g[:0]).to(dev_s).contiguous())
+
+    def partition_dense_parameters(self, names):
+        from .hash_utils import string_to_id
+        out = {s: [] for s in range(self.S)}
+        for n in names:
+            out[string_to_id(n, self.S)].append(n)
+        return out
