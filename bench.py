@@ -345,7 +345,7 @@ def run_b200_arm(a):
         e2e = {"value": B * world * a.e2e_steps / (float(t2.item()) * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": runner.h2d_bytes, "d2h_bytes_per_step": runner.d2h_bytes,
                "ms_per_step": float(t2.item()) / a.e2e_steps,
-               "path": "HostStepRunner: ids H2D -> lookup -> emb D2H -> grad H2D -> dedup + update -> n_unique D2H"}
+               "path": "HostStepRunner: ids H2D -> lookup -> emb D2H (stream 1) || grad H2D (stream 2) -> dedup + update -> n_unique D2H"}
 
     clocks = sampler.result() if sampler else None
 
