@@ -124,8 +124,11 @@ k_rowscan(uint32_t* __restrict__ hist, int n_tiles, uint32_t* __restrict__ tot) 
 }
 
 // ------------------------------------------------------------------ pass kernel 3: scatter
+// All global inputs of the tile (keys, payloads, digit totals, this tile's scanned counts) are
+// requested up front so their latencies overlap; digit and rank share one register per key.
+// 6 CTAs per SM keep the 832 tiles of a cfg2 batch in a single wave.
 template <typename KeyT, typename Loader, typename DigitFn, typename KeyOutT>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 6)
 k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
           const uint32_t* __restrict__ hist, const uint32_t* __restrict__ tot,
           KeyOutT* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
@@ -134,11 +137,22 @@ k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
   __shared__ unsigned warp_sum[kWarps];
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const int64_t ne = eff_n(n, n_dev);
+  const int64_t wbeg = (int64_t)blockIdx.x * kTile + w * (32 * kItems);
+  // ---- issue every global load first
+  const unsigned t = tot[tid];
+  const unsigned tile_off = hist[(size_t)tid * n_tiles + blockIdx.x];
+  KeyT key[kItems];
+  uint32_t val[kItems];
+#pragma unroll
+  for (int k = 0; k < kItems; ++k) {
+    const int64_t j = wbeg + k * 32 + lane;
+    if (j < ne) { key[k] = ld.key(j); val[k] = ld.val(j); }
+    else { key[k] = (KeyT)0; val[k] = 0u; }
+  }
 #pragma unroll
   for (int i = 0; i < kWarps; ++i) cnt[i][tid] = 0;
 
   // global digit base: exclusive scan over the 256 digit totals (thread d <-> digit d)
-  unsigned t = tot[tid];
   unsigned inc = t;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -157,28 +171,25 @@ k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
     if (tid == n_bins) offsets_out[tid] = (int32_t)ne;
   }
 
-  const int64_t wbeg = (int64_t)blockIdx.x * kTile + w * (32 * kItems);
-  KeyT key[kItems];
-  unsigned dig[kItems], rank[kItems];
+  unsigned dr[kItems];   // digit in bits 0..8 (256 = invalid), rank within the warp's digit run above
   const unsigned lt = edl_lanemask_lt();
 #pragma unroll
   for (int k = 0; k < kItems; ++k) {
-    int64_t j = wbeg + k * 32 + lane;
-    bool valid = j < ne;
-    key[k] = valid ? ld.key(j) : (KeyT)0;
-    dig[k] = valid ? dg(key[k], j) : 256u;
-    unsigned mask = __match_any_sync(0xffffffffu, dig[k]);
-    int leader = __ffs(mask) - 1;
+    const int64_t j = wbeg + k * 32 + lane;
+    const bool valid = j < ne;
+    const unsigned d = valid ? dg(key[k], j) : 256u;
+    const unsigned mask = __match_any_sync(0xffffffffu, d);
+    const int leader = __ffs(mask) - 1;
     unsigned prev = 0;
-    if (lane == leader && valid) prev = cnt[w][dig[k]];
+    if (lane == leader && valid) prev = cnt[w][d];
     prev = __shfl_sync(0xffffffffu, prev, leader);
-    rank[k] = prev + __popc(mask & lt);
-    if (lane == leader && valid) cnt[w][dig[k]] = prev + __popc(mask);
+    dr[k] = d | ((prev + __popc(mask & lt)) << 9);
+    if (lane == leader && valid) cnt[w][d] = prev + __popc(mask);
     __syncwarp();
   }
   __syncthreads();
   {
-    unsigned run = dbase + hist[(size_t)tid * n_tiles + blockIdx.x];
+    unsigned run = dbase + tile_off;
 #pragma unroll
     for (int i = 0; i < kWarps; ++i) {
       unsigned c = cnt[i][tid];
@@ -189,13 +200,12 @@ k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < kItems; ++k) {
-    int64_t j = wbeg + k * 32 + lane;
-    if (j < ne) {
-      unsigned p = cnt[w][dig[k]] + rank[k];
-      uint32_t v = ld.val(j);
+    const unsigned d = dr[k] & 511u;
+    if (d < 256u) {
+      const unsigned p = cnt[w][d] + (dr[k] >> 9);
       keys_out[p] = (KeyOutT)key[k];
-      vals_out[p] = v;
-      if (pos_out) pos_out[v] = (int32_t)p;
+      vals_out[p] = val[k];
+      if (pos_out) pos_out[val[k]] = (int32_t)p;
     }
   }
 }
