@@ -7,7 +7,8 @@
 
 namespace {
 
-constexpr int kLongThr = 16;   // segments longer than this go through the chunk path
+constexpr int kLongThrMin = 2;  // smallest allowed threshold (sizes the scratch)
+constexpr int kLongThrDefault = 16;  // segments longer than this go through the chunk path
 constexpr int kChunk = 64;     // gradient rows per chunk
 constexpr int kUnrollD = 4;    // independent row loads in flight per lane group (short path)
 constexpr int kUnrollC = 4;    // same, chunk path
@@ -21,20 +22,20 @@ struct DirectWs {
 };
 
 // kMode: 0 every segment; 1 only ids that occur once; 2 only ids that occur more than once
-template <int kG, int kC, typename GT, typename Epi, int kMinBlocks = 4, int kUnroll = kUnrollD, int kMode = 0>
-__global__ void __launch_bounds__(kThreads, kMinBlocks)
+template <int kG, int kC, typename GT, typename Epi, int kMinBlocks = 4, int kUnroll = kUnrollD, int kMode = 0, int kBlock = kThreads>
+__global__ void __launch_bounds__(kBlock, kMinBlocks)
 k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __restrict__ order,
              const int32_t* __restrict__ seg, const int32_t* __restrict__ seg_first,
              const int32_t* __restrict__ n_unique,
              const int64_t* __restrict__ uniq, const int64_t* __restrict__ layout, Epi epi,
              int32_t* __restrict__ counters, int32_t* __restrict__ long_list,
-             int32_t* __restrict__ chunk_list) {
+             int32_t* __restrict__ chunk_list, int kLongThr) {
   __shared__ EdlLayoutSmem L;
   typedef Row<GT> R;
   edl_layout_load(&L, layout);
   __syncthreads();
   const int U = *n_unique;
-  const int u = (int)(((int64_t)blockIdx.x * kThreads + threadIdx.x) / kG);
+  const int u = (int)(((int64_t)blockIdx.x * kBlock + threadIdx.x) / kG);
   const int gl = threadIdx.x % kG;
   if (u >= U) return;
   const int s0 = seg[u], s1 = seg[u + 1];
@@ -277,12 +278,24 @@ int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t*
                   const int64_t* layout, Epi epi, const DirectWs& W, cudaStream_t st) {
   const int64_t ctas = edl_cdiv(max_unique * kG, kThreads);
   EDL_REQUIRE(ctas < 0x7fffffff, EDL_ELIMIT, "segreduce: max_unique=%lld too large", (long long)max_unique);
+  static int long_thr = -1;
+  if (long_thr < 0) {
+    const char* e = getenv("EDL_LONG_THR");
+    long_thr = e ? std::max(kLongThrMin, atoi(e)) : kLongThrDefault;
+  }
   // 8 CTAs x 256 threads per SM (<= 32 registers) and one row in flight per lane group: measured
   // faster than fewer, fatter threads (profiles/r1_direct_variants.md) -- the loads that hide HBM
   // latency come from occupancy, not from unrolling.
-  k_seg_direct<kG, kC, GT, Epi, (kC == 1 ? 8 : 4), 1><<<(unsigned)ctas, kThreads, 0, st>>>(
-      (const unsigned char*)grad, D4, order, seg, seg_first, n_unique, uniq, layout, epi, W.counters, W.long_list,
-      W.chunk_list);
+  static int blk = -1;
+  if (blk < 0) { const char* e = getenv("EDL_DIRECT_BLOCK"); blk = e ? atoi(e) : 256; }
+#define EDL_DARGS (const unsigned char*)grad, D4, order, seg, seg_first, n_unique, uniq, layout, epi, W.counters, W.long_list, W.chunk_list, long_thr
+  if (kC == 1 && blk == 64)
+    k_seg_direct<kG, kC, GT, Epi, 32, 1, 0, 64><<<(unsigned)edl_cdiv(max_unique * kG, 64), 64, 0, st>>>(EDL_DARGS);
+  else if (kC == 1 && blk == 128)
+    k_seg_direct<kG, kC, GT, Epi, 16, 1, 0, 128><<<(unsigned)edl_cdiv(max_unique * kG, 128), 128, 0, st>>>(EDL_DARGS);
+  else
+    k_seg_direct<kG, kC, GT, Epi, (kC == 1 ? 8 : 4), 1><<<(unsigned)ctas, kThreads, 0, st>>>(EDL_DARGS);
+#undef EDL_DARGS
   const int64_t gc = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_chunks * kG, kThreads), EDL_SM_COUNT * 4));
   k_seg_chunk<kG, kC, GT, Epi><<<(unsigned)gc, kThreads, 0, st>>>((const unsigned char*)grad, D4, order, seg,
                                                                   W.counters, W.chunk_list, W.long_list, W.partial,

@@ -29,7 +29,7 @@ Ws carve_ws(void* ws, int64_t n_rows, int dim) {
   w.tile.carry_h = (double*)(p + off); off += (size_t)kMaxGrid * dim * sizeof(double);
   w.tile.carry_t = (double*)(p + off); off += (size_t)kMaxGrid * dim * sizeof(double);
   const int64_t n = n_rows > 0 ? n_rows : 0;
-  w.direct.max_long = n / (kLongThr + 1) + 1;
+  w.direct.max_long = n / (kLongThrMin + 1) + 1;
   w.direct.max_chunks = n / kChunk + w.direct.max_long + 1;
   w.direct.long_list = (int32_t*)(p + off); off = edl_align_up(off + (size_t)w.direct.max_long * 4 * 4, 256);
   w.direct.chunk_list = (int32_t*)(p + off); off = edl_align_up(off + (size_t)w.direct.max_chunks * 2 * 4, 256);
