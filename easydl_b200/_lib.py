@@ -36,9 +36,9 @@ PROTOTYPES = {
     "edl_last_error_string": (C.c_char_p, []),
     "edl_init_rows": (_int, [_p, _int, _p, _i64, _i64, C.c_uint64, _p]),
     "edl_fill_f32": (_int, [_p, _i64, C.c_float, _p]),
-    "edl_unique_workspace_bytes": (_sz, [_i64, _int]),
-    "edl_unique": (_int, [_p, _i64, _p, _p, _int, _int, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
-    "edl_unique_static": (_int, [_p, _i64, _p, _p, _int, _int, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "edl_unique_workspace_bytes": (_sz, [_i64, _int, _int, _int]),
+    "edl_unique": (_int, [_p, _i64, _p, _p, _int, _int, _int, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "edl_unique_static": (_int, [_p, _i64, _p, _p, _int, _int, _int, _p, _p, _p, _p, _p, _p, _p, _p]),
     "edl_partition_mod_workspace_bytes": (_sz, [_i64, _int]),
     "edl_partition_mod": (_int, [_p, _i64, _p, _p, _int, _p, _p, _p, _p, _p, _sz, _p]),
     "edl_gather_keys": (_int, [_p, _int, _p, _i64, _p, _p, _p, _p]),

@@ -33,6 +33,32 @@ struct IdsLoader {  // pass 0 of the sort: fused key formed on the fly, payload 
   __device__ __forceinline__ uint32_t val(int64_t j) const { return (uint32_t)j; }
 };
 
+// Field-major pass 0 (fused [B, F] id batches): element j' = f * stride + b reads ids[b * F + f].
+// Keys are the per-field ids (the field is the segment, see Seg), payload = batch position.
+template <typename KeyT>
+struct FieldMajorLoader {
+  const int64_t* ids;
+  int n_fields;
+  int64_t stride;   // padded samples per field
+  __device__ __forceinline__ KeyT key(int64_t jp) const {
+    const int64_t f = jp / stride, b = jp - f * stride;
+    return (KeyT)ids[b * n_fields + f];
+  }
+  __device__ __forceinline__ uint32_t val(int64_t jp) const {
+    const int64_t f = jp / stride, b = jp - f * stride;
+    return (uint32_t)(b * n_fields + f);
+  }
+};
+
+// Segmented counting sort: the tiles are grouped into independent segments (one per field) that
+// are sorted separately and stay in segment order.  tps == 0: one segment, the flat case.
+struct Seg {
+  int tps;             // tiles per segment (0 = all tiles form one segment)
+  int64_t in_stride;   // distance between segment starts in the input index space
+  int64_t valid;       // valid elements at the start of every segment
+  int64_t out_stride;  // distance between segment starts in the output index space
+};
+
 template <typename KeyT>
 struct PairLoader {  // later passes
   const KeyT* keys;
@@ -71,17 +97,21 @@ __device__ __forceinline__ int64_t eff_n(int64_t n, const int32_t* n_dev) {
 // ------------------------------------------------------------------ pass kernel 1: histogram
 template <typename KeyT, typename Loader, typename DigitFn>
 __global__ void __launch_bounds__(kThreads)
-k_hist(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles, uint32_t* __restrict__ hist) {
+k_hist(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles, uint32_t* __restrict__ hist,
+       Seg sg) {
   __shared__ unsigned h[256];
   const int tid = threadIdx.x;
   h[tid] = 0;
   __syncthreads();
-  const int64_t ne = eff_n(n, n_dev);
-  const int64_t base = (int64_t)blockIdx.x * kTile;
+  const int f = sg.tps ? (int)blockIdx.x / sg.tps : 0;
+  const int lt = sg.tps ? (int)blockIdx.x % sg.tps : (int)blockIdx.x;
+  const int64_t ne = sg.tps ? sg.valid : eff_n(n, n_dev);
+  const int64_t sbase = (int64_t)f * sg.in_stride;
+  const int64_t base = (int64_t)lt * kTile;
 #pragma unroll
   for (int k = 0; k < kItems; ++k) {
     int64_t j = base + k * kThreads + tid;
-    if (j < ne) atomicAdd(&h[dg(ld.key(j), j)], 1u);
+    if (j < ne) atomicAdd(&h[dg(ld.key(sbase + j), sbase + j)], 1u);
   }
   __syncthreads();
   hist[(size_t)tid * n_tiles + blockIdx.x] = h[tid];
@@ -90,13 +120,16 @@ k_hist(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles, uint
 // ------------------------------------------------------------------ pass kernel 2: row scan
 // One CTA per digit: exclusive scan of its row of per-tile counts, in place; row total out.
 __global__ void __launch_bounds__(kThreads)
-k_rowscan(uint32_t* __restrict__ hist, int n_tiles, uint32_t* __restrict__ tot) {
+k_rowscan(uint32_t* __restrict__ hist, int n_tiles, uint32_t* __restrict__ tot, int tps) {
   __shared__ unsigned warp_sum[kWarps];
-  uint32_t* row = hist + (size_t)blockIdx.x * n_tiles;
+  // blockIdx.x = f * 256 + digit; the row piece of segment f is [f * tps, (f + 1) * tps)
+  const int d = (int)blockIdx.x & 255, f = (int)blockIdx.x >> 8;
+  const int len = tps ? tps : n_tiles;
+  uint32_t* row = hist + (size_t)d * n_tiles + (size_t)f * len;
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  const int per = (n_tiles + kThreads - 1) / kThreads;
+  const int per = (len + kThreads - 1) / kThreads;
   const int b = tid * per;
-  const int e = min(b + per, n_tiles);
+  const int e = min(b + per, len);
   unsigned s = 0;
   for (int i = b; i < e; ++i) s += row[i];
   unsigned inc = s;
@@ -132,21 +165,24 @@ __global__ void __launch_bounds__(kThreads, 6)
 k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
           const uint32_t* __restrict__ hist, const uint32_t* __restrict__ tot,
           KeyOutT* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
-          int32_t* __restrict__ pos_out, int32_t* __restrict__ offsets_out, int n_bins) {
+          int32_t* __restrict__ pos_out, int32_t* __restrict__ offsets_out, int n_bins, Seg sg) {
   __shared__ unsigned cnt[kWarps][256];
   __shared__ unsigned warp_sum[kWarps];
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  const int64_t ne = eff_n(n, n_dev);
-  const int64_t wbeg = (int64_t)blockIdx.x * kTile + w * (32 * kItems);
+  const int f = sg.tps ? (int)blockIdx.x / sg.tps : 0;
+  const int ltile = sg.tps ? (int)blockIdx.x % sg.tps : (int)blockIdx.x;
+  const int64_t ne = sg.tps ? sg.valid : eff_n(n, n_dev);
+  const int64_t sbase = (int64_t)f * sg.in_stride;
+  const int64_t wbeg = (int64_t)ltile * kTile + w * (32 * kItems);
   // ---- issue every global load first
-  const unsigned t = tot[tid];
+  const unsigned t = tot[f * 256 + tid];
   const unsigned tile_off = hist[(size_t)tid * n_tiles + blockIdx.x];
   KeyT key[kItems];
   uint32_t val[kItems];
 #pragma unroll
   for (int k = 0; k < kItems; ++k) {
     const int64_t j = wbeg + k * 32 + lane;
-    if (j < ne) { key[k] = ld.key(j); val[k] = ld.val(j); }
+    if (j < ne) { key[k] = ld.key(sbase + j); val[k] = ld.val(sbase + j); }
     else { key[k] = (KeyT)0; val[k] = 0u; }
   }
 #pragma unroll
@@ -177,7 +213,7 @@ k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
   for (int k = 0; k < kItems; ++k) {
     const int64_t j = wbeg + k * 32 + lane;
     const bool valid = j < ne;
-    const unsigned d = valid ? dg(key[k], j) : 256u;
+    const unsigned d = valid ? dg(key[k], sbase + j) : 256u;
     const unsigned mask = __match_any_sync(0xffffffffu, d);
     const int leader = __ffs(mask) - 1;
     unsigned prev = 0;
@@ -189,7 +225,7 @@ k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
   }
   __syncthreads();
   {
-    unsigned run = dbase + tile_off;
+    unsigned run = dbase + tile_off + (unsigned)((int64_t)f * sg.out_stride);
 #pragma unroll
     for (int i = 0; i < kWarps; ++i) {
       unsigned c = cnt[i][tid];
@@ -213,7 +249,8 @@ k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
 // ------------------------------------------------------------------ unique kernels
 template <typename KeyT>
 __global__ void __launch_bounds__(kThreads)
-k_head_count(const KeyT* __restrict__ keys, int64_t n, const int32_t* n_dev, uint32_t* __restrict__ tile_heads) {
+k_head_count(const KeyT* __restrict__ keys, int64_t n, const int32_t* n_dev, uint32_t* __restrict__ tile_heads,
+             int64_t seg_len) {
   __shared__ unsigned warp_sum[kWarps];
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const int64_t ne = eff_n(n, n_dev);
@@ -222,7 +259,7 @@ k_head_count(const KeyT* __restrict__ keys, int64_t n, const int32_t* n_dev, uin
 #pragma unroll
   for (int k = 0; k < kItems; ++k) {
     int64_t i = base + k * kThreads + tid;
-    if (i < ne) c += (i == 0 || keys[i] != keys[i - 1]) ? 1u : 0u;
+    if (i < ne) c += (i == 0 || keys[i] != keys[i - 1] || (seg_len && i % seg_len == 0)) ? 1u : 0u;
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
@@ -277,7 +314,8 @@ __global__ void __launch_bounds__(kThreads)
 k_unique_write(const KeyT* __restrict__ keys, const uint32_t* __restrict__ order, int64_t n,
                const int32_t* n_dev, const uint32_t* __restrict__ tile_base,
                int64_t* __restrict__ uniq, int32_t* __restrict__ seg_offsets,
-               int32_t* __restrict__ seg_first, int32_t* __restrict__ inverse) {
+               int32_t* __restrict__ seg_first, int32_t* __restrict__ inverse, int64_t seg_len,
+               const int64_t* __restrict__ field_base) {
   __shared__ unsigned warp_sum[kWarps];
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const int64_t ne = eff_n(n, n_dev);
@@ -292,7 +330,7 @@ k_unique_write(const KeyT* __restrict__ keys, const uint32_t* __restrict__ order
     int64_t i = base + k;
     bool valid = i < ne;
     key[k] = valid ? keys[i] : (KeyT)0;
-    flag[k] = (valid && (i == 0 || key[k] != prev)) ? 1u : 0u;
+    flag[k] = (valid && (i == 0 || key[k] != prev || (seg_len && i % seg_len == 0))) ? 1u : 0u;
     prev = key[k];
     c += flag[k];
   }
@@ -316,7 +354,7 @@ k_unique_write(const KeyT* __restrict__ keys, const uint32_t* __restrict__ order
       run += flag[k];
       unsigned u = run - 1;
       if (flag[k]) {
-        uniq[u] = (int64_t)key[k];
+        uniq[u] = (int64_t)key[k] + (seg_len ? field_base[i / seg_len] : 0);
         seg_offsets[u] = (int32_t)i;
         if (seg_first) seg_first[u] = (int32_t)order[i];
       }
@@ -355,20 +393,51 @@ __global__ void k_empty_unique(int32_t* n_unique, int32_t* seg_offsets) {
 
 // ------------------------------------------------------------------ workspace carving
 struct UniqueWs {
-  void* keysA; void* keysB; uint32_t* valsB; uint32_t* hist; uint32_t* tot; uint32_t* tile_heads;
+  void* keysA; void* keysB; uint32_t* valsA; uint32_t* valsB; uint32_t* hist; uint32_t* tot; uint32_t* tile_heads;
   size_t bytes;
 };
 
-UniqueWs carve_unique(void* ws, int64_t n, int key_bits) {
-  const size_t kb = key_bits <= 32 ? 4 : 8;
-  const int64_t tiles = edl_cdiv(n > 0 ? n : 1, kTile);
+// Field-major mode (fused [B, F] batches): sort every field's ids separately on their own
+// `field_bits` instead of the fused key's `key_bits` -- the field is known from the position, so
+// its bits need no radix pass (cfg2: 24 instead of 28 bits = 3 passes instead of 4).
+struct FmPlan { bool on; int F; int64_t B, Bp; int tpf; };
+
+FmPlan fm_plan(int64_t n, const int32_t* n_dev, const int64_t* field_base, int n_fields, int key_bits,
+               int field_bits) {
+  FmPlan f{false, 1, n, n, 0};
+  if (field_bits <= 0 || !field_base || n_fields <= 1 || n_dev || n % n_fields != 0) return f;
+  if ((field_bits + 7) / 8 >= (key_bits + 7) / 8) return f;   // no pass saved
+  f.on = true;
+  f.F = n_fields;
+  f.B = n / n_fields;
+  f.tpf = (int)edl_cdiv(f.B, kTile);
+  f.Bp = (int64_t)f.tpf * kTile;
+  return f;
+}
+
+UniqueWs carve_unique(void* ws, int64_t n, int key_bits, int n_fields, int field_bits) {
+  // sized for either mode: field-major pads every field to whole tiles
+  int64_t cap = n;
+  int64_t tiles = edl_cdiv(n > 0 ? n : 1, kTile);
+  int tot_rows = 1;
+  bool fm_possible = false;
+  if (field_bits > 0 && n_fields > 1 && n % n_fields == 0) {
+    fm_possible = true;
+    const int64_t tpf = edl_cdiv(n / n_fields, kTile);
+    cap = std::max<int64_t>(cap, tpf * kTile * n_fields);
+    tiles = std::max<int64_t>(tiles, tpf * n_fields);
+    tot_rows = n_fields;
+  }
+  const size_t kb = (key_bits <= 32 || (field_bits > 0 && field_bits <= 32 && n_fields > 1)) && key_bits <= 32 ? 4 : 8;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = edl_align_up(off + bytes, 256); return o; };
-  size_t oA = take((size_t)n * kb), oB = take((size_t)n * kb), oV = take((size_t)n * 4);
-  size_t oH = take((size_t)256 * tiles * 4), oT = take(256 * 4), oC = take((size_t)(tiles + 1) * 4);
+  // the flat sort ping-pongs its payload between `order` and valsB; only the padded field-major
+  // sort needs a second scratch payload buffer
+  size_t oA = take((size_t)cap * kb), oB = take((size_t)cap * kb), oVA = take(fm_possible ? (size_t)cap * 4 : 0), oVB = take((size_t)cap * 4);
+  size_t oH = take((size_t)256 * tiles * 4), oT = take((size_t)256 * 4 * tot_rows), oC = take((size_t)(tiles + 1) * 4);
   UniqueWs r;
   char* p = (char*)ws;
-  r.keysA = p + oA; r.keysB = p + oB; r.valsB = (uint32_t*)(p + oV);
+  r.keysA = p + oA; r.keysB = p + oB; r.valsA = (uint32_t*)(p + oVA); r.valsB = (uint32_t*)(p + oVB);
   r.hist = (uint32_t*)(p + oH); r.tot = (uint32_t*)(p + oT); r.tile_heads = (uint32_t*)(p + oC);
   r.bytes = off;
   return r;
@@ -376,40 +445,54 @@ UniqueWs carve_unique(void* ws, int64_t n, int key_bits) {
 
 template <typename KeyT>
 int unique_impl(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64_t* field_base,
-                int n_fields, int key_bits, int64_t* uniq, int32_t* inverse, int32_t* counts,
-                int32_t* order, int32_t* seg_offsets, int32_t* seg_first, int32_t* n_unique,
-                const UniqueWs& W, cudaStream_t st) {
-  const int tiles = (int)edl_cdiv(n, kTile);
-  const int passes = (key_bits + 7) / 8;
+                int n_fields, int key_bits, int field_bits, int64_t* uniq, int32_t* inverse,
+                int32_t* counts, int32_t* order, int32_t* seg_offsets, int32_t* seg_first,
+                int32_t* n_unique, const UniqueWs& W, cudaStream_t st) {
+  const FmPlan fm = fm_plan(n, n_dev, field_base, n_fields, key_bits, field_bits);
+  const int sort_tiles = fm.on ? fm.F * fm.tpf : (int)edl_cdiv(n, kTile);
+  const int passes = ((fm.on ? field_bits : key_bits) + 7) / 8;
+  const int n_seg = fm.on ? fm.F : 1;
   KeyT* kbuf[2] = {(KeyT*)W.keysA, (KeyT*)W.keysB};
-  uint32_t* vbuf[2];
-  // the last pass must land the payload in `order`
-  vbuf[(passes - 1) & 1] = (uint32_t*)order;
-  vbuf[(passes & 1)] = W.valsB;
+  uint32_t* vbuf[2] = {W.valsA, W.valsB};
+  if (!fm.on) {   // flat: `order` is one of the two payload buffers, placed so the last pass lands in it
+    vbuf[(passes - 1) & 1] = (uint32_t*)order;
+    vbuf[passes & 1] = W.valsB;
+  }
   for (int p = 0; p < passes; ++p) {
+    const bool last = p == passes - 1;
     BitDigit<KeyT> dg{p * 8};
     KeyT* ko = kbuf[p & 1];
-    uint32_t* vo = vbuf[p & 1];
-    if (p == 0) {
+    uint32_t* vo = last ? (uint32_t*)order : vbuf[p & 1];   // the last pass lands the payload in `order`
+    Seg sg{0, 0, 0, 0};
+    if (fm.on) sg = Seg{fm.tpf, fm.Bp, fm.B, last ? fm.B : fm.Bp};
+    if (p == 0 && fm.on) {
+      FieldMajorLoader<KeyT> ld{ids, fm.F, fm.Bp};
+      k_hist<KeyT><<<sort_tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, sort_tiles, W.hist, sg);
+      k_rowscan<<<256 * n_seg, kThreads, 0, st>>>(W.hist, sort_tiles, W.tot, sg.tps);
+      k_scatter<KeyT><<<sort_tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, sort_tiles, W.hist, W.tot, ko, vo,
+                                                       (int32_t*)nullptr, (int32_t*)nullptr, 0, sg);
+    } else if (p == 0) {
       IdsLoader<KeyT> ld{ids, field_base, n_fields};
-      k_hist<KeyT><<<tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, tiles, W.hist);
-      k_rowscan<<<256, kThreads, 0, st>>>(W.hist, tiles, W.tot);
-      k_scatter<KeyT><<<tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, tiles, W.hist, W.tot, ko, vo,
-                                                  (int32_t*)nullptr, (int32_t*)nullptr, 0);
+      k_hist<KeyT><<<sort_tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, sort_tiles, W.hist, sg);
+      k_rowscan<<<256 * n_seg, kThreads, 0, st>>>(W.hist, sort_tiles, W.tot, sg.tps);
+      k_scatter<KeyT><<<sort_tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, sort_tiles, W.hist, W.tot, ko, vo,
+                                                       (int32_t*)nullptr, (int32_t*)nullptr, 0, sg);
     } else {
       PairLoader<KeyT> ld{kbuf[(p - 1) & 1], vbuf[(p - 1) & 1]};
-      k_hist<KeyT><<<tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, tiles, W.hist);
-      k_rowscan<<<256, kThreads, 0, st>>>(W.hist, tiles, W.tot);
-      k_scatter<KeyT><<<tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, tiles, W.hist, W.tot, ko, vo,
-                                                  (int32_t*)nullptr, (int32_t*)nullptr, 0);
+      k_hist<KeyT><<<sort_tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, sort_tiles, W.hist, sg);
+      k_rowscan<<<256 * n_seg, kThreads, 0, st>>>(W.hist, sort_tiles, W.tot, sg.tps);
+      k_scatter<KeyT><<<sort_tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, sort_tiles, W.hist, W.tot, ko, vo,
+                                                       (int32_t*)nullptr, (int32_t*)nullptr, 0, sg);
     }
   }
   EDL_LAUNCH_CHECK("radix passes");
+  const int tiles = (int)edl_cdiv(n, kTile);
   const KeyT* sorted = kbuf[(passes - 1) & 1];
-  k_head_count<KeyT><<<tiles, kThreads, 0, st>>>(sorted, n, n_dev, W.tile_heads);
+  const int64_t seg_len = fm.on ? fm.B : 0;
+  k_head_count<KeyT><<<tiles, kThreads, 0, st>>>(sorted, n, n_dev, W.tile_heads, seg_len);
   k_scan_tiles<<<1, 1024, 0, st>>>(W.tile_heads, tiles, n, n_dev, n_unique, seg_offsets);
-  k_unique_write<KeyT><<<tiles, kThreads, 0, st>>>(sorted, (const uint32_t*)order, n, n_dev,
-                                                   W.tile_heads, uniq, seg_offsets, seg_first, inverse);
+  k_unique_write<KeyT><<<tiles, kThreads, 0, st>>>(sorted, (const uint32_t*)order, n, n_dev, W.tile_heads, uniq,
+                                                   seg_offsets, seg_first, inverse, seg_len, field_base);
   if (counts) {
     int g = (int)std::min<int64_t>(edl_cdiv(n, 256), EDL_SM_COUNT * 8);
     k_counts<<<g, 256, 0, st>>>(seg_offsets, n_unique, counts);
@@ -418,21 +501,29 @@ int unique_impl(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64
   return EDL_OK;
 }
 
+// key width of the sort: 32-bit keys when the bits that are actually sorted fit
+bool sort_keys_32(int64_t n, const int32_t* n_dev, const int64_t* field_base, int n_fields, int key_bits,
+                  int field_bits) {
+  const FmPlan fm = fm_plan(n, n_dev, field_base, n_fields, key_bits, field_bits);
+  return (fm.on ? field_bits : key_bits) <= 32;
+}
+
 }  // namespace
 
-extern "C" size_t edl_unique_workspace_bytes(int64_t n, int key_bits) {
+extern "C" size_t edl_unique_workspace_bytes(int64_t n, int key_bits, int n_fields, int field_bits) {
   if (n < 0) return 0;
-  return carve_unique(nullptr, n, key_bits).bytes;
+  return carve_unique(nullptr, n, key_bits, n_fields, field_bits).bytes;
 }
 
 extern "C" int edl_unique(const int64_t* ids, int64_t n, const int32_t* n_dev,
-                          const int64_t* field_base, int n_fields, int key_bits, int64_t* uniq,
-                          int32_t* inverse, int32_t* counts, int32_t* order, int32_t* seg_offsets,
-                          int32_t* seg_first, int32_t* n_unique, void* workspace,
-                          size_t workspace_bytes, edl_stream_t stream) {
+                          const int64_t* field_base, int n_fields, int key_bits, int field_bits,
+                          int64_t* uniq, int32_t* inverse, int32_t* counts, int32_t* order,
+                          int32_t* seg_offsets, int32_t* seg_first, int32_t* n_unique,
+                          void* workspace, size_t workspace_bytes, edl_stream_t stream) {
   cudaStream_t st = (cudaStream_t)stream;
   EDL_REQUIRE(n >= 0 && n < (int64_t)0x7fff0000, EDL_EINVAL, "edl_unique: n=%lld out of range", (long long)n);
   EDL_REQUIRE(key_bits >= 1 && key_bits <= 64, EDL_EINVAL, "edl_unique: key_bits=%d not in 1..64", key_bits);
+  EDL_REQUIRE(field_bits >= 0 && field_bits <= 64, EDL_EINVAL, "edl_unique: field_bits=%d not in 0..64", field_bits);
   EDL_REQUIRE(seg_offsets && n_unique, EDL_EINVAL, "edl_unique: seg_offsets and n_unique are required");
   EDL_REQUIRE(!field_base || n_fields > 0, EDL_EINVAL, "edl_unique: n_fields must be > 0 with field_base");
   if (n == 0) {
@@ -442,13 +533,13 @@ extern "C" int edl_unique(const int64_t* ids, int64_t n, const int32_t* n_dev,
   }
   EDL_REQUIRE(uniq && order, EDL_EINVAL, "edl_unique: uniq and order are required");
   EDL_REQUIRE(ids, EDL_EINVAL, "edl_unique: ids is null");
-  UniqueWs W = carve_unique(workspace, n, key_bits);
+  UniqueWs W = carve_unique(workspace, n, key_bits, n_fields, field_bits);
   EDL_REQUIRE(workspace && workspace_bytes >= W.bytes, EDL_EWORKSPACE,
               "edl_unique: workspace %zu < required %zu", workspace_bytes, W.bytes);
-  if (key_bits <= 32)
-    return unique_impl<uint32_t>(ids, n, n_dev, field_base, n_fields, key_bits, uniq, inverse, counts,
+  if (sort_keys_32(n, n_dev, field_base, n_fields, key_bits, field_bits))
+    return unique_impl<uint32_t>(ids, n, n_dev, field_base, n_fields, key_bits, field_bits, uniq, inverse, counts,
                                  order, seg_offsets, seg_first, n_unique, W, st);
-  return unique_impl<uint64_t>(ids, n, n_dev, field_base, n_fields, key_bits, uniq, inverse, counts,
+  return unique_impl<uint64_t>(ids, n, n_dev, field_base, n_fields, key_bits, field_bits, uniq, inverse, counts,
                                order, seg_offsets, seg_first, n_unique, W, st);
 }
 
@@ -498,10 +589,11 @@ extern "C" int edl_partition_mod(const int64_t* keys, int64_t n, const int32_t* 
   k_shard_digits<<<g, kThreads, 0, st>>>(keys, n, n_dev, layout, (unsigned)num_shards, W.dig);
   KeyIndexLoader ld{keys};
   ArrayDigit dg{W.dig};
-  k_hist<int64_t><<<tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, tiles, W.hist);
-  k_rowscan<<<256, kThreads, 0, st>>>(W.hist, tiles, W.tot);
+  const Seg flat{0, 0, 0, 0};
+  k_hist<int64_t><<<tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, tiles, W.hist, flat);
+  k_rowscan<<<256, kThreads, 0, st>>>(W.hist, tiles, W.tot, 0);
   k_scatter<int64_t><<<tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, tiles, W.hist, W.tot, keys_out,
-                                                 (uint32_t*)perm, pos, offsets, num_shards);
+                                                 (uint32_t*)perm, pos, offsets, num_shards, flat);
   EDL_LAUNCH_CHECK("partition kernels");
   return EDL_OK;
 }
@@ -543,7 +635,7 @@ int static_scratch(void** out) {
 
 extern "C" int edl_unique_static(const int64_t* ids, int64_t n, const int32_t* n_dev,
                                  const int64_t* field_base, int n_fields, int key_bits,
-                                 int64_t* uniq, int32_t* inverse, int32_t* counts, int32_t* order,
+                                 int field_bits, int64_t* uniq, int32_t* inverse, int32_t* counts, int32_t* order,
                                  int32_t* seg_offsets, int32_t* seg_first, int32_t* n_unique,
                                  edl_stream_t stream) {
   cudaStream_t st = (cudaStream_t)stream;
@@ -564,16 +656,17 @@ extern "C" int edl_unique_static(const int64_t* ids, int64_t n, const int32_t* n
   void* scratch = nullptr;
   int rc = static_scratch(&scratch);
   if (rc) return rc;
-  UniqueWs W = carve_unique(scratch, n, key_bits);
+  EDL_REQUIRE(field_bits >= 0 && field_bits <= 64, EDL_EINVAL, "edl_unique_static: field_bits=%d not in 0..64", field_bits);
+  UniqueWs W = carve_unique(scratch, n, key_bits, n_fields, field_bits);
   EDL_REQUIRE(W.bytes <= (size_t)EDL_UNIQUE_STATIC_SCRATCH_BYTES, EDL_ELIMIT,
               "edl_unique_static: n=%lld at key_bits=%d needs %zu scratch bytes, the built-in array has %d",
               (long long)n, key_bits, W.bytes, EDL_UNIQUE_STATIC_SCRATCH_BYTES);
   // Nothing in the scratch has to start at zero: every histogram cell, digit total and tile
   // count is written by this call before this call reads it, so whatever the previous call
   // left behind is never observed.
-  if (key_bits <= 32)
-    return unique_impl<uint32_t>(ids, n, n_dev, field_base, n_fields, key_bits, uniq, inverse, counts,
+  if (sort_keys_32(n, n_dev, field_base, n_fields, key_bits, field_bits))
+    return unique_impl<uint32_t>(ids, n, n_dev, field_base, n_fields, key_bits, field_bits, uniq, inverse, counts,
                                  order, seg_offsets, seg_first, n_unique, W, st);
-  return unique_impl<uint64_t>(ids, n, n_dev, field_base, n_fields, key_bits, uniq, inverse, counts,
+  return unique_impl<uint64_t>(ids, n, n_dev, field_base, n_fields, key_bits, field_bits, uniq, inverse, counts,
                                order, seg_offsets, seg_first, n_unique, W, st);
 }

@@ -85,7 +85,7 @@ class UniqueResult:
 
 
 def unique(ids: torch.Tensor, field_base: Optional[torch.Tensor] = None, key_bits: int = 64, *,
-           want_inverse: bool = True, want_counts: bool = True,
+           field_bits: int = 0, want_inverse: bool = True, want_counts: bool = True,
            n_dev: Optional[torch.Tensor] = None, out: Optional[UniqueResult] = None,
            workspace: Optional[torch.Tensor] = None) -> UniqueResult:
     lib = _lib.load()
@@ -105,10 +105,10 @@ def unique(ids: torch.Tensor, field_base: Optional[torch.Tensor] = None, key_bit
             seg_offsets=torch.empty(n + 1, dtype=torch.int32, device=dev),
             n_unique=torch.empty(1, dtype=torch.int32, device=dev), n=n,
             seg_first=torch.empty(max(n, 1), dtype=torch.int32, device=dev))
-    need = lib.edl_unique_workspace_bytes(n, key_bits)
+    need = lib.edl_unique_workspace_bytes(n, key_bits, n_fields, field_bits)
     if workspace is None or workspace.numel() < need:
         workspace = _ws(need, dev)
-    check(lib.edl_unique(_ptr(ids), n, _ptr(n_dev), _ptr(field_base), n_fields, key_bits,
+    check(lib.edl_unique(_ptr(ids), n, _ptr(n_dev), _ptr(field_base), n_fields, key_bits, field_bits,
                          _ptr(out.uniq), _ptr(out.inverse), _ptr(out.counts), _ptr(out.order),
                          _ptr(out.seg_offsets), _ptr(out.seg_first), _ptr(out.n_unique),
                          _ptr(workspace), workspace.numel(), _stream()), "edl_unique")

@@ -52,6 +52,11 @@ class ShardLayout:
     def key_bits(self) -> int:
         return max(1, int(self.total_rows - 1).bit_length())
 
+    @property
+    def field_bits(self) -> int:
+        """Bits of the largest per-table id (the radix sort of a fused batch runs on these)."""
+        return max(1, int(max(self.rows) - 1).bit_length())
+
     def to_array(self) -> np.ndarray:
         """[T, S, shard, 0, key_base[T+1], local_base[T+1]] as the kernels expect."""
         T = self.n_tables

@@ -36,7 +36,8 @@ class CudaOps:
         self.dim = params.dim
 
     def unique(self, flat_ids):
-        return K.unique(flat_ids, self.field_base, self.key_bits, want_inverse=True, want_counts=False)
+        return K.unique(flat_ids, self.field_base, self.key_bits, field_bits=self.params.layout.field_bits,
+                        want_inverse=True, want_counts=False)
 
     def partition(self, uq, num_shards: int):
         return K.partition_mod(uq.uniq, self.layout_dev, num_shards, n_dev=uq.n_unique)

@@ -29,6 +29,7 @@ class SparseStep:
         lib = _lib.load()
         self.field_base = torch.from_numpy(params.layout.key_base[:self.F].copy()).to(dev)
         self.key_bits = params.layout.key_bits
+        self.field_bits = params.layout.field_bits
         N, D = self.N, params.dim
         self.emb = torch.empty((N, D), dtype=torch.float32, device=dev)
         self.uq = K.UniqueResult(
@@ -37,11 +38,12 @@ class SparseStep:
             seg_offsets=torch.empty(N + 1, dtype=torch.int32, device=dev),
             n_unique=torch.zeros(1, dtype=torch.int32, device=dev), n=N,
             seg_first=torch.empty(N, dtype=torch.int32, device=dev))
-        self.ws_unique = torch.empty(lib.edl_unique_workspace_bytes(N, self.key_bits),
+        self.ws_unique = torch.empty(lib.edl_unique_workspace_bytes(N, self.key_bits, self.F, self.field_bits),
                                      dtype=torch.uint8, device=dev)
         self.ws_seg = torch.empty(lib.edl_segreduce_workspace_bytes(N, N, D), dtype=torch.uint8, device=dev)
         # launches per step (for bench.py's gpu_launches): gather 1; unique 3/pass + 3; update 2 + memset
-        self.launches_per_step = 1 + 3 * ((self.key_bits + 7) // 8) + 3 + 3  # + one memset node
+        passes = min((self.key_bits + 7) // 8, (self.field_bits + 7) // 8)
+        self.launches_per_step = 1 + 3 * passes + 3 + 3  # + one memset node
         self.last_n_unique = self.uq.n_unique
 
     def lookup(self, ids: torch.Tensor) -> torch.Tensor:
@@ -49,8 +51,8 @@ class SparseStep:
         return K.gather_ids(self.params.slab, ids.view(-1), self.field_base, out=self.emb)
 
     def dedup(self, ids: torch.Tensor) -> K.UniqueResult:
-        return K.unique(ids.view(-1), self.field_base, self.key_bits, want_inverse=False,
-                        want_counts=False, out=self.uq, workspace=self.ws_unique)
+        return K.unique(ids.view(-1), self.field_base, self.key_bits, field_bits=self.field_bits,
+                        want_inverse=False, want_counts=False, out=self.uq, workspace=self.ws_unique)
 
     def update(self, ids: torch.Tensor, grad: torch.Tensor, uq: Optional[K.UniqueResult] = None):
         """grad f32 [B*F, dim]: upstream gradient of emb."""

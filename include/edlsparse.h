@@ -72,11 +72,14 @@ int edl_fill_f32(float* dst, int64_t n, float value, edl_stream_t stream);
  *   id: lets the reduce kernels skip one dependent load for ids that occur once,
  *   n_unique: device int32 scalar U.
  * Only the low key_bits bits of the keys may be non-zero (1..64).
+ * field_bits (0 = off): for a fused [B, F] batch (n = B * n_fields, field_base ascending) the
+ * ids of one field fit field_bits bits; the sort then runs per field on those bits only -- the
+ * field is known from the position and needs no radix pass.  Same outputs either way.
  * n_dev (nullable): device int32 holding the actual n (<= n); used when the input length
  * itself was produced on the device. */
-size_t edl_unique_workspace_bytes(int64_t n, int key_bits);
+size_t edl_unique_workspace_bytes(int64_t n, int key_bits, int n_fields, int field_bits);
 int edl_unique(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64_t* field_base,
-               int n_fields, int key_bits, int64_t* uniq, int32_t* inverse, int32_t* counts,
+               int n_fields, int key_bits, int field_bits, int64_t* uniq, int32_t* inverse, int32_t* counts,
                int32_t* order, int32_t* seg_offsets, int32_t* seg_first, int32_t* n_unique,
                void* workspace, size_t workspace_bytes, edl_stream_t stream);
 
@@ -107,7 +110,7 @@ int edl_unique(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64_
 #define EDL_UNIQUE_STATIC_MAX_IDS 131072
 #define EDL_UNIQUE_STATIC_SCRATCH_BYTES (3 * 1024 * 1024)
 int edl_unique_static(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64_t* field_base,
-                      int n_fields, int key_bits, int64_t* uniq, int32_t* inverse, int32_t* counts,
+                      int n_fields, int key_bits, int field_bits, int64_t* uniq, int32_t* inverse, int32_t* counts,
                       int32_t* order, int32_t* seg_offsets, int32_t* seg_first, int32_t* n_unique,
                       edl_stream_t stream);
 

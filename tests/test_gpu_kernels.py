@@ -98,6 +98,29 @@ def test_unique_fused_fields_equals_per_table(cuda):
     assert np.array_equal(uniq, cat)
 
 
+@pytest.mark.parametrize("B,rows", [(1, [5, 9]), (37, [1000, 50, 7777, 3]), (2048, [300, 300, 70000]),
+                                    (2049, [1 << 20, 11]), (5000, [10_000_000] * 26), (4096, [40_000_000] * 5)])
+def test_unique_field_major_mode(cuda, B, rows):
+    """field_bits > 0: per-field sort on the per-field id bits -- identical outputs to the flat sort."""
+    from easydl_b200 import kernels as K
+    from easydl_b200.criteo import CriteoSynthetic
+    ids = CriteoSynthetic(rows, B, 1.05).ids(1)
+    bases = O.key_bases(rows)
+    keys = O.fuse_keys(ids, bases)
+    key_bits = int(bases[-1] - 1).bit_length()
+    field_bits = max(1, int(max(rows) - 1).bit_length())
+    r = K.unique(dev(ids, cuda).view(-1), dev(bases[:len(rows)], cuda), key_bits, field_bits=field_bits)
+    U = r.count()
+    uniq, inv, cnt, order, seg = O.dedup(keys)
+    assert U == len(uniq)
+    assert np.array_equal(r.uniq[:U].cpu().numpy(), uniq)
+    assert np.array_equal(r.inverse.cpu().numpy(), inv)
+    assert np.array_equal(r.counts[:U].cpu().numpy(), cnt)
+    assert np.array_equal(r.order.cpu().numpy(), order)
+    assert np.array_equal(r.seg_offsets[:U + 1].cpu().numpy(), seg)
+    assert np.array_equal(r.seg_first[:U].cpu().numpy(), order[seg[:-1]])
+
+
 def test_unique_n_dev(cuda):
     from easydl_b200 import kernels as K
     rng = np.random.default_rng(5)

@@ -37,7 +37,7 @@ def _call_static(lib, ids, field_base, key_bits):
     fb_ptr = None if field_base is None else field_base.data_ptr()
     nf = 0 if field_base is None else field_base.numel()
     rc = lib.edl_unique_static(
-        ids.data_ptr() if n else None, n, None, fb_ptr, nf, key_bits,
+        ids.data_ptr() if n else None, n, None, fb_ptr, nf, key_bits, 0,
         out["uniq"].data_ptr(), out["inverse"].data_ptr(), out["counts"].data_ptr(),
         out["order"].data_ptr(), out["seg"].data_ptr(), out["first"].data_ptr(), out["nu"].data_ptr(),
         torch.cuda.current_stream().cuda_stream)
