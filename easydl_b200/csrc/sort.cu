@@ -25,12 +25,13 @@ struct IdsLoader {  // pass 0 of the sort: fused key formed on the fly, payload 
   const int64_t* ids;
   const int64_t* field_base;
   int n_fields;
-  __device__ __forceinline__ KeyT key(int64_t j) const {
+  __device__ __forceinline__ KeyT key(int, int64_t j) const {
     long long k = ids[j];
     if (field_base) k += field_base[(int)(j % n_fields)];
     return (KeyT)k;
   }
-  __device__ __forceinline__ uint32_t val(int64_t j) const { return (uint32_t)j; }
+  __device__ __forceinline__ uint32_t val(int, int64_t j) const { return (uint32_t)j; }
+  __device__ __forceinline__ int64_t flat(int, int64_t j) const { return j; }
 };
 
 // Field-major pass 0 (fused [B, F] id batches): element j' = f * stride + b reads ids[b * F + f].
@@ -40,14 +41,9 @@ struct FieldMajorLoader {
   const int64_t* ids;
   int n_fields;
   int64_t stride;   // padded samples per field
-  __device__ __forceinline__ KeyT key(int64_t jp) const {
-    const int64_t f = jp / stride, b = jp - f * stride;
-    return (KeyT)ids[b * n_fields + f];
-  }
-  __device__ __forceinline__ uint32_t val(int64_t jp) const {
-    const int64_t f = jp / stride, b = jp - f * stride;
-    return (uint32_t)(b * n_fields + f);
-  }
+  __device__ __forceinline__ KeyT key(int f, int64_t b) const { return (KeyT)ids[b * n_fields + f]; }
+  __device__ __forceinline__ uint32_t val(int f, int64_t b) const { return (uint32_t)(b * n_fields + f); }
+  __device__ __forceinline__ int64_t flat(int f, int64_t b) const { return (int64_t)f * stride + b; }
 };
 
 // Segmented counting sort: the tiles are grouped into independent segments (one per field) that
@@ -63,14 +59,17 @@ template <typename KeyT>
 struct PairLoader {  // later passes
   const KeyT* keys;
   const uint32_t* vals;
-  __device__ __forceinline__ KeyT key(int64_t j) const { return keys[j]; }
-  __device__ __forceinline__ uint32_t val(int64_t j) const { return vals[j]; }
+  int64_t stride;   // distance between segment starts (0: flat)
+  __device__ __forceinline__ KeyT key(int f, int64_t j) const { return keys[(int64_t)f * stride + j]; }
+  __device__ __forceinline__ uint32_t val(int f, int64_t j) const { return vals[(int64_t)f * stride + j]; }
+  __device__ __forceinline__ int64_t flat(int f, int64_t j) const { return (int64_t)f * stride + j; }
 };
 
 struct KeyIndexLoader {  // partition: int64 key, payload = position
   const int64_t* keys;
-  __device__ __forceinline__ int64_t key(int64_t j) const { return keys[j]; }
-  __device__ __forceinline__ uint32_t val(int64_t j) const { return (uint32_t)j; }
+  __device__ __forceinline__ int64_t key(int, int64_t j) const { return keys[j]; }
+  __device__ __forceinline__ uint32_t val(int, int64_t j) const { return (uint32_t)j; }
+  __device__ __forceinline__ int64_t flat(int, int64_t j) const { return j; }
 };
 
 template <typename KeyT>
@@ -106,12 +105,11 @@ k_hist(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles, uint
   const int f = sg.tps ? (int)blockIdx.x / sg.tps : 0;
   const int lt = sg.tps ? (int)blockIdx.x % sg.tps : (int)blockIdx.x;
   const int64_t ne = sg.tps ? sg.valid : eff_n(n, n_dev);
-  const int64_t sbase = (int64_t)f * sg.in_stride;
   const int64_t base = (int64_t)lt * kTile;
 #pragma unroll
   for (int k = 0; k < kItems; ++k) {
     int64_t j = base + k * kThreads + tid;
-    if (j < ne) atomicAdd(&h[dg(ld.key(sbase + j), sbase + j)], 1u);
+    if (j < ne) atomicAdd(&h[dg(ld.key(f, j), ld.flat(f, j))], 1u);
   }
   __syncthreads();
   hist[(size_t)tid * n_tiles + blockIdx.x] = h[tid];
@@ -156,6 +154,26 @@ k_rowscan(uint32_t* __restrict__ hist, int n_tiles, uint32_t* __restrict__ tot, 
   if (tid == 0) tot[blockIdx.x] = total;
 }
 
+// Segmented variant for short row pieces (tps <= 32: one lane per tile): one WARP per
+// (segment, digit) instead of one CTA.  blockDim = 256 -> 8 row pieces per CTA.
+__global__ void __launch_bounds__(kThreads)
+k_rowscan_warp(uint32_t* __restrict__ hist, int n_tiles, uint32_t* __restrict__ tot, int tps, int n_rows) {
+  const int r = (int)blockIdx.x * kWarps + (threadIdx.x >> 5);   // r = f * 256 + digit
+  if (r >= n_rows) return;
+  const int lane = threadIdx.x & 31;
+  const int d = r & 255, f = r >> 8;
+  uint32_t* row = hist + (size_t)d * n_tiles + (size_t)f * tps;
+  const unsigned v = lane < tps ? row[lane] : 0u;
+  unsigned inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    unsigned x = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += x;
+  }
+  if (lane < tps) row[lane] = inc - v;
+  if (lane == 31) tot[r] = inc;
+}
+
 // ------------------------------------------------------------------ pass kernel 3: scatter
 // All global inputs of the tile (keys, payloads, digit totals, this tile's scanned counts) are
 // requested up front so their latencies overlap; digit and rank share one register per key.
@@ -172,7 +190,6 @@ k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
   const int f = sg.tps ? (int)blockIdx.x / sg.tps : 0;
   const int ltile = sg.tps ? (int)blockIdx.x % sg.tps : (int)blockIdx.x;
   const int64_t ne = sg.tps ? sg.valid : eff_n(n, n_dev);
-  const int64_t sbase = (int64_t)f * sg.in_stride;
   const int64_t wbeg = (int64_t)ltile * kTile + w * (32 * kItems);
   // ---- issue every global load first
   const unsigned t = tot[f * 256 + tid];
@@ -182,7 +199,7 @@ k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
 #pragma unroll
   for (int k = 0; k < kItems; ++k) {
     const int64_t j = wbeg + k * 32 + lane;
-    if (j < ne) { key[k] = ld.key(sbase + j); val[k] = ld.val(sbase + j); }
+    if (j < ne) { key[k] = ld.key(f, j); val[k] = ld.val(f, j); }
     else { key[k] = (KeyT)0; val[k] = 0u; }
   }
 #pragma unroll
@@ -213,7 +230,7 @@ k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
   for (int k = 0; k < kItems; ++k) {
     const int64_t j = wbeg + k * 32 + lane;
     const bool valid = j < ne;
-    const unsigned d = valid ? dg(key[k], sbase + j) : 256u;
+    const unsigned d = valid ? dg(key[k], ld.flat(f, j)) : 256u;
     const unsigned mask = __match_any_sync(0xffffffffu, d);
     const int leader = __ffs(mask) - 1;
     unsigned prev = 0;
@@ -443,6 +460,13 @@ UniqueWs carve_unique(void* ws, int64_t n, int key_bits, int n_fields, int field
   return r;
 }
 
+void rowscan(uint32_t* hist, int n_tiles, uint32_t* tot, int tps, int n_seg, cudaStream_t st) {
+  if (tps > 0 && tps <= 32)
+    k_rowscan_warp<<<(256 * n_seg + kWarps - 1) / kWarps, kThreads, 0, st>>>(hist, n_tiles, tot, tps, 256 * n_seg);
+  else
+    k_rowscan<<<256 * n_seg, kThreads, 0, st>>>(hist, n_tiles, tot, tps);
+}
+
 template <typename KeyT>
 int unique_impl(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64_t* field_base,
                 int n_fields, int key_bits, int field_bits, int64_t* uniq, int32_t* inverse,
@@ -468,19 +492,19 @@ int unique_impl(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64
     if (p == 0 && fm.on) {
       FieldMajorLoader<KeyT> ld{ids, fm.F, fm.Bp};
       k_hist<KeyT><<<sort_tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, sort_tiles, W.hist, sg);
-      k_rowscan<<<256 * n_seg, kThreads, 0, st>>>(W.hist, sort_tiles, W.tot, sg.tps);
+      rowscan(W.hist, sort_tiles, W.tot, sg.tps, n_seg, st);
       k_scatter<KeyT><<<sort_tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, sort_tiles, W.hist, W.tot, ko, vo,
                                                        (int32_t*)nullptr, (int32_t*)nullptr, 0, sg);
     } else if (p == 0) {
       IdsLoader<KeyT> ld{ids, field_base, n_fields};
       k_hist<KeyT><<<sort_tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, sort_tiles, W.hist, sg);
-      k_rowscan<<<256 * n_seg, kThreads, 0, st>>>(W.hist, sort_tiles, W.tot, sg.tps);
+      rowscan(W.hist, sort_tiles, W.tot, sg.tps, n_seg, st);
       k_scatter<KeyT><<<sort_tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, sort_tiles, W.hist, W.tot, ko, vo,
                                                        (int32_t*)nullptr, (int32_t*)nullptr, 0, sg);
     } else {
-      PairLoader<KeyT> ld{kbuf[(p - 1) & 1], vbuf[(p - 1) & 1]};
+      PairLoader<KeyT> ld{kbuf[(p - 1) & 1], vbuf[(p - 1) & 1], fm.on ? fm.Bp : 0};
       k_hist<KeyT><<<sort_tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, sort_tiles, W.hist, sg);
-      k_rowscan<<<256 * n_seg, kThreads, 0, st>>>(W.hist, sort_tiles, W.tot, sg.tps);
+      rowscan(W.hist, sort_tiles, W.tot, sg.tps, n_seg, st);
       k_scatter<KeyT><<<sort_tiles, kThreads, 0, st>>>(ld, dg, n, n_dev, sort_tiles, W.hist, W.tot, ko, vo,
                                                        (int32_t*)nullptr, (int32_t*)nullptr, 0, sg);
     }
