@@ -54,6 +54,8 @@ def parse_args():
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
     ap.add_argument("--force-sharded", action="store_true",
                     help="N=1 only: run the multi-shard code path (dedup/partition/exchange/expand) with S=1")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N>1: all-to-all-v by NVLink peer writes (CUDA IPC) or by NCCL")
     ap.add_argument("--wire", default="f64", choices=["f64", "f32"],
                     help="element type of exchanged partial gradient sums (N>1)")
     return ap.parse_args()
@@ -219,9 +221,16 @@ def run_b200_arm(a):
         step = SparseStep(params, B)
     else:
         from easydl_b200.sharded_step import ShardedSparseStep
-        from easydl_b200.exchange import SingleExchange, TorchExchange
-        ex = TorchExchange(dist.group.WORLD, dev) if world > 1 else SingleExchange()
-        step = ShardedSparseStep(params, B, ex, wire_dtype=torch.float64 if a.wire == "f64" else torch.float32)
+        from easydl_b200.exchange import PeerExchange, SingleExchange, TorchExchange
+        wire_dtype = torch.float64 if a.wire == "f64" else torch.float32
+        if world == 1:
+            ex = SingleExchange()
+        elif a.exchange == "peer":
+            # receive buffers sized for 1.5x the balanced share of unique ids (hash-mod spreads evenly)
+            ex = PeerExchange(dist.group.WORLD, dev, int(1.5 * N), D, wire_dtype)
+        else:
+            ex = TorchExchange(dist.group.WORLD, dev)
+        step = ShardedSparseStep(params, B, ex, wire_dtype=wire_dtype)
 
     # distinct batches per rank: step index = batch_no * world + rank
     src = CriteoSynthetic(rows, B, a.alpha)
@@ -361,6 +370,7 @@ def run_b200_arm(a):
                        "unique_per_step": U_mean, "sharding": f"row-wise id mod {world}",
                        "code_path": "sharded" if sharded else "single-shard fused",
                        "gradient_wire": a.wire if sharded else None,
+                       "exchange": (a.exchange if world > 1 else None),
                        "cache": "inputs larger than L2: 133 GB of table rows touched at random, "
                                 f"{nb} id batches cycled, 436 MB gradient + 436 MB output per step"},
             "gpu_launches": step.launches_per_step * a.steps,

@@ -54,6 +54,13 @@ PROTOTYPES = {
     "edl_export_shard": (_int, [_p, _p, _p, _int, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "edl_import_shard": (_int, [_p, _p, _p, _int, _p, _p, _p, _p, _p, _p, _i64, _p]),
     "edl_scatter_rows": (_int, [_p, _int, _p, _i64, _p, _p, _p]),
+    "edl_peer_alloc": (_int, [C.POINTER(C.c_void_p), _sz]),
+    "edl_peer_free": (_int, [_p]),
+    "edl_ipc_export": (_int, [_p, C.c_char_p]),
+    "edl_ipc_import": (_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "edl_ipc_close": (_int, [_p]),
+    "edl_peer_copy": (_int, [_p, _p, _sz, _p]),
+    "edl_peer_signal_wait": (_int, [_p, _p, _int, _int, _i64, _p]),
 }
 
 _lib = None

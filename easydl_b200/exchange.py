@@ -10,8 +10,16 @@ Steps are written as generators that `yield` exchange requests, so the same step
 Requests:
   ("counts", t)                 t: int64 [W, k] on the step's device; row r goes to rank r.
                                 -> int64 [W, k] HOST tensor, row r = what rank r sent us.
-  ("a2av", t, send, recv)       t: [sum(send), ...]; send/recv: per-rank row counts (lists).
+  ("a2av", t, send, recv[, direction, tag])
+                                t: [sum(send), ...]; send/recv: per-rank row counts (lists).
                                 -> [sum(recv), ...]
+                                direction "fwd" = the pattern of the last counts round, "rev" = its
+                                transpose (answers travelling back); tag names the receive buffer.
+                                Both are hints for PeerExchange; the other drivers ignore them.
+
+PeerExchange replaces the NCCL all-to-all-v by direct writes into the peers' receive buffers over
+NVLink (CUDA IPC mapped memory): measured on 2 B200s the three NCCL all-to-all-v rounds of a step
+took 1.17 ms of a 2.28 ms step at ~300 GB/s; a peer copy of the same bytes runs at link speed.
 """
 from __future__ import annotations
 
@@ -48,7 +56,7 @@ class TorchExchange:
             self.dist.all_to_all_single(out, t, group=self.group)
             return out.cpu()  # the one host synchronisation of an exchange round
         if kind == "a2av":
-            _, t, send, recv = req
+            t, send, recv = req[1], req[2], req[3]
             t = t.contiguous()
             out = torch.empty((int(sum(recv)),) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
             self.dist.all_to_all_single(out, t, output_split_sizes=[int(x) for x in recv],
@@ -116,3 +124,132 @@ def run_lockstep(gens: Sequence[Generator]) -> List:
             except StopIteration as stop:
                 results[r], live[r] = stop.value, False
     return results
+
+
+class _RawDeviceMemory:
+    """Lets torch view a raw device pointer (zero copy) through __cuda_array_interface__."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False),
+                                         "version": 2}
+
+
+class PeerExchange:
+    """All-to-all-v by peer writes.  Every rank owns one receive buffer (two generations, used
+    alternately step by step, so a fast rank that has already started the next step never
+    overwrites what a slow rank is still reading); the buffers are mapped into every other rank
+    with CUDA IPC at set-up.  A round = each rank copies its S slices straight into the S
+    receivers' buffers at the offsets implied by the gathered count matrix, then one tiny NCCL
+    all-reduce orders "all writes issued" before "any read" on every rank's stream."""
+
+    REGIONS = ("keys", "rows", "grads")
+
+    def __init__(self, group, device, capacity_rows: int, dim: int, wire_dtype=torch.float64):
+        import ctypes as C
+
+        import torch.distributed as dist
+
+        from . import _lib
+        self.lib = _lib.load()
+        self.C, self.dist, self.group = C, dist, group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.device = torch.device(device)
+        self.cap = int(capacity_rows)
+        wire_b = 8 if wire_dtype == torch.float64 else 4
+        self.row_bytes = {"keys": 8, "rows": dim * 4, "grads": dim * wire_b}
+        self.dtypes = {"keys": torch.int64, "rows": torch.float32, "grads": wire_dtype}
+        self.dim = dim
+        self.region_off, off = {}, 0
+        for gen in (0, 1):
+            for r in self.REGIONS:
+                self.region_off[(gen, r)] = off
+                off += (self.cap * self.row_bytes[r] + 255) // 256 * 256
+        self.flags_off = off                       # [world + 1] int64 arrival counters, then padding
+        off += 1024
+        self.nbytes = off
+        ptr = C.c_void_p()
+        _lib.check(self.lib.edl_peer_alloc(C.byref(ptr), self.nbytes), "edl_peer_alloc")
+        self.own_ptr = ptr.value
+        handle = C.create_string_buffer(64)
+        _lib.check(self.lib.edl_ipc_export(self.own_ptr, handle), "edl_ipc_export")
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle.raw), group=group)
+        self.base = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                self.base.append(self.own_ptr)
+            else:
+                p = C.c_void_p()
+                _lib.check(self.lib.edl_ipc_import(h, C.byref(p)), "edl_ipc_import")
+                self.base.append(p.value)
+        self.own = torch.as_tensor(_RawDeviceMemory(self.own_ptr, self.nbytes), device=self.device)
+        self.flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.own_flags = self.own[self.flags_off:self.flags_off + 8 * (self.world + 1)].view(torch.int64)
+        self.peer_flag_ptrs = torch.tensor([b + self.flags_off for b in self.base], dtype=torch.int64,
+                                           device=self.device)
+        self.round = 0
+        self.gen = 1
+        self.M = None          # [W, W] rows sent s -> d in the current step
+        dist.barrier(group=group)
+
+    def close(self):
+        for r, p in enumerate(self.base):
+            if r != self.rank and p:
+                self.lib.edl_ipc_close(p)
+        self.lib.edl_peer_free(self.own_ptr)
+        self.base, self.own_ptr = [], None
+
+    def _fence(self):
+        """Order "every rank has issued its writes of this round" before "any rank reads"."""
+        self.round += 1
+        rc = self.lib.edl_peer_signal_wait(self.peer_flag_ptrs.data_ptr(), self.own_flags.data_ptr(),
+                                           self.rank, self.world, self.round,
+                                           torch.cuda.current_stream().cuda_stream)
+        if rc:
+            from . import _lib
+            _lib.check(rc, "edl_peer_signal_wait")
+
+    def handle(self, req):
+        kind = req[0]
+        if kind == "counts":
+            t = req[1].contiguous()
+            allc = torch.empty((self.world,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+            self.dist.all_gather_into_tensor(allc, t, group=self.group)
+            allc = allc.cpu()                                   # [src, dst, k]: the step's one host sync
+            self.M = allc[:, :, 0].clone()
+            self.gen ^= 1
+            return allc[:, self.rank].contiguous()
+        if kind != "a2av":
+            raise ValueError(f"unknown exchange request {kind!r}")
+        t, send, recv = req[1].contiguous(), req[2], req[3]
+        direction = req[4] if len(req) > 4 else "fwd"
+        tag = req[5] if len(req) > 5 else None
+        if tag not in self.row_bytes or t.dtype != self.dtypes[tag]:
+            raise ValueError(f"PeerExchange: no receive buffer for tag {tag!r} / dtype {t.dtype}")
+        rb = self.row_bytes[tag]
+        if t.numel() and t.element_size() * (t.numel() // t.shape[0]) != rb:
+            raise ValueError("PeerExchange: row size does not match the receive buffer")
+        n_recv = int(sum(recv))
+        if n_recv > self.cap:
+            raise RuntimeError(f"PeerExchange: {n_recv} rows to receive, buffer holds {self.cap}")
+        M = self.M if direction == "fwd" else self.M.t()
+        me, st = self.rank, torch.cuda.current_stream().cuda_stream
+        roff = self.region_off[(self.gen, tag)]
+        soff = 0
+        for d in range(self.world):
+            n = int(send[d])
+            if n:
+                dst_row = int(M[:me, d].sum())                  # rows that lower ranks put before mine
+                rc = self.lib.edl_peer_copy(self.base[d] + roff + dst_row * rb, t.data_ptr() + soff * rb,
+                                            n * rb, st)
+                if rc:
+                    from . import _lib
+                    _lib.check(rc, "edl_peer_copy")
+            soff += n
+        self._fence()
+        out = self.own[roff:roff + n_recv * rb].view(self.dtypes[tag])
+        return out if tag == "keys" else out.view(n_recv, -1)
+
+    def run(self, gen: Generator):
+        return _drive(gen, self.handle)

@@ -96,9 +96,9 @@ class ShardedSparseStep:
         send = [int(x) for x in counts.cpu().reshape(-1)]
         recv = [int(x) for x in got.reshape(-1)]
         U = sum(send)
-        recv_keys = yield ("a2av", part.keys[:U], send, recv)
+        recv_keys = yield ("a2av", part.keys[:U], send, recv, "fwd", "keys")
         rows_out = self.ops.lookup(recv_keys)
-        rows_in = yield ("a2av", rows_out, recv, send)       # [U, D], partition order
+        rows_in = yield ("a2av", rows_out, recv, send, "rev", "rows")   # [U, D], partition order
         emb = self.ops.expand(rows_in, uq, part)
         self._fw = (uq, part, send, recv, recv_keys, U)
         self.last_n_unique = uq.n_unique
@@ -107,7 +107,7 @@ class ShardedSparseStep:
     def gen_update(self, grad: torch.Tensor) -> Generator:
         uq, part, send, recv, recv_keys, U = self._fw
         g_send = self.ops.reduce_for_send(grad, uq, part, U, self.wire_dtype)
-        g_recv = yield ("a2av", g_send, send, recv)          # aligned with recv_keys
+        g_recv = yield ("a2av", g_send, send, recv, "fwd", "grads")   # aligned with recv_keys
         self.ops.apply(recv_keys, g_recv)
         return None
 

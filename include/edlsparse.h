@@ -206,6 +206,26 @@ int edl_import_shard(float* slab, float* slot0, float* slot1, int dim, uint32_t*
 int edl_scatter_rows(const float* rows, int dim, const int32_t* pos, int64_t n,
                      const int32_t* n_dev, float* out, edl_stream_t stream);
 
+/* ---- A7 over NVLink peer memory (replaces the worker <-> PS RPC of the lineage) ----------
+ * Exchange buffers that the other ranks of the box write into directly.  Set-up: every rank
+ * allocates its receive buffer (edl_peer_alloc: the one place this library allocates, because a
+ * CUDA IPC handle exists only for a whole cudaMalloc allocation), exports a 64-byte handle
+ * (edl_ipc_export), ships it to its peers by any host channel, and maps theirs
+ * (edl_ipc_import).  Per step: edl_peer_copy into the mapped pointers (NVLink), or kernels of
+ * this library given a mapped pointer as their output. */
+int edl_peer_alloc(void** ptr, size_t bytes);
+int edl_peer_free(void* ptr);
+int edl_ipc_export(void* ptr, unsigned char* handle64);
+int edl_ipc_import(const unsigned char* handle64, void** ptr);
+int edl_ipc_close(void* ptr);
+int edl_peer_copy(void* dst, const void* src, size_t bytes, edl_stream_t stream);
+/* One kernel per rank that closes an exchange round: publishes `value` into slot `me` of every
+ * peer's flag array (peer_flag_ptrs_dev: device array of `world` mapped pointers), then waits
+ * until all `world` slots of own_flags hold >= value.  own_flags has world + 1 entries; entry
+ * [world] is set to -1 if the wait timed out.  One rank per GPU. */
+int edl_peer_signal_wait(const int64_t* peer_flag_ptrs_dev, int64_t* own_flags, int me, int world,
+                         int64_t value, edl_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
