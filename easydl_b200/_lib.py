@@ -46,7 +46,7 @@ PROTOTYPES = {
     "edl_expand": (_int, [_p, _int, _p, _i64, _p, _p]),
     "edl_compose_index": (_int, [_p, _p, _i64, _p, _p]),
     "edl_segreduce_workspace_bytes": (_sz, [_i64, _i64, _int]),
-    "edl_segreduce": (_int, [_p, _int, _p, _p, _p, _p, _i64, _i64, _p, _p, _int, _p, _sz, _p]),
+    "edl_segreduce": (_int, [_p, _int, _p, _p, _p, _p, _i64, _i64, _p, _p, _int, _p, _p, _sz, _p]),
     "edl_segreduce_update": (_int, [_p, _p, _p, _int, _p, _p, _p, _p, _p, _i64, _i64, _p, _int, _p,
                                     C.POINTER(OptParams), _p, _p, _sz, _p]),
     "edl_export_workspace_bytes": (_sz, [_i64]),

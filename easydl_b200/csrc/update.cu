@@ -94,20 +94,23 @@ extern "C" int edl_segreduce(const float* grad, int dim, const int32_t* order,
                              const int32_t* seg_offsets, const int32_t* seg_first,
                              const int32_t* n_unique_dev,
                              int64_t max_unique, int64_t n_rows, const int32_t* out_pos, void* g_out, int out_f64,
-                             void* workspace, size_t workspace_bytes, edl_stream_t stream) {
+                             const int64_t* dst_table, void* workspace, size_t workspace_bytes,
+                             edl_stream_t stream) {
   if (max_unique == 0) return EDL_OK;
   Ws W;
   int rc = check_common("edl_segreduce", grad, dim, order, seg_offsets, n_unique_dev, max_unique, n_rows,
                         workspace, workspace_bytes, &W);
   if (rc) return rc;
-  EDL_REQUIRE(g_out && (((uintptr_t)g_out) & 15) == 0, EDL_EINVAL, "edl_segreduce: g_out null or misaligned");
+  EDL_REQUIRE(dst_table || (g_out && (((uintptr_t)g_out) & 15) == 0), EDL_EINVAL,
+              "edl_segreduce: g_out null or misaligned (and no dst_table)");
+  EDL_REQUIRE(!dst_table || out_pos, EDL_EINVAL, "edl_segreduce: dst_table needs out_pos");
   cudaStream_t st = (cudaStream_t)stream;
   if (out_f64) {
-    EpiWrite64 epi{(double*)g_out, out_pos};
+    EpiWrite64 epi{(double*)g_out, out_pos, dst_table};
     return dispatch_dim<float, EpiWrite64>(grad, dim, order, seg_offsets, seg_first, n_unique_dev, max_unique, nullptr,
                                            nullptr, epi, W, st);
   }
-  EpiWrite epi{(float4*)g_out, out_pos};
+  EpiWrite epi{(float4*)g_out, out_pos, dst_table};
   return dispatch_dim<float, EpiWrite>(grad, dim, order, seg_offsets, seg_first, n_unique_dev, max_unique, nullptr,
                                        nullptr, epi, W, st);
 }

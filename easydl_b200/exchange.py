@@ -248,8 +248,41 @@ class PeerExchange:
                     _lib.check(rc, "edl_peer_copy")
             soff += n
         self._fence()
+        return self._recv_view(tag, n_recv)
+
+    def _recv_view(self, tag, n_recv):
+        rb, roff = self.row_bytes[tag], self.region_off[(self.gen, tag)]
         out = self.own[roff:roff + n_recv * rb].view(self.dtypes[tag])
         return out if tag == "keys" else out.view(n_recv, -1)
+
+    # ---- fused pack -> send: kernels write straight into the receivers' buffers
+    def remote_rows(self, tag: str, direction: str, dst: int, n_rows: int):
+        """A tensor view of the slice of rank `dst`'s receive buffer that this rank fills in the
+        current round (peer-mapped memory: stores to it travel over NVLink)."""
+        rb = self.row_bytes[tag]
+        M = self.M if direction == "fwd" else self.M.t()
+        dst_row = int(M[:self.rank, dst].sum())
+        ptr = self.base[dst] + self.region_off[(self.gen, tag)] + dst_row * rb
+        t = torch.as_tensor(_RawDeviceMemory(ptr, max(n_rows * rb, 1)), device=self.device)
+        return t[:n_rows * rb].view(self.dtypes[tag]).view(n_rows, -1)
+
+    def dst_table(self, tag: str, direction: str, offsets):
+        """Destination table for a fused reduce -> send (kernels.segreduce dst_table): group s of
+        the partition order goes to rank s's receive buffer, after the rows of lower ranks."""
+        rb = self.row_bytes[tag]
+        M = self.M if direction == "fwd" else self.M.t()
+        roff = self.region_off[(self.gen, tag)]
+        bases = [self.base[d] + roff + int(M[:self.rank, d].sum()) * rb for d in range(self.world)]
+        t = [self.world] + [int(x) for x in offsets] + bases
+        return torch.tensor(t, dtype=torch.int64, device=self.device)
+
+    def finish_round(self, tag: str, recv):
+        """Close a round whose data was written by kernels (remote_rows): fence, then the view."""
+        n_recv = int(sum(recv))
+        if n_recv > self.cap:
+            raise RuntimeError(f"PeerExchange: {n_recv} rows to receive, buffer holds {self.cap}")
+        self._fence()
+        return self._recv_view(tag, n_recv)
 
     def run(self, gen: Generator):
         return _drive(gen, self.handle)

@@ -209,24 +209,27 @@ def segreduce(grad: torch.Tensor, order: torch.Tensor, seg_offsets: torch.Tensor
               n_unique: torch.Tensor, max_unique: int, *, seg_first: Optional[torch.Tensor] = None,
               out_pos: Optional[torch.Tensor] = None,
               out: Optional[torch.Tensor] = None, out_dtype=torch.float32,
+              dst_table: Optional[torch.Tensor] = None,
               workspace: Optional[torch.Tensor] = None):
-    """g[dst(u)] = float64 segment sum; out_dtype float32 (rounded once) or float64 (exact wire)."""
+    """g[dst(u)] = float64 segment sum; out_dtype float32 (rounded once) or float64 (exact wire).
+    dst_table: fused reduce -> send, rows are written to per-group base addresses (see the header)."""
     lib = _lib.load()
     _need(grad, torch.float32, "grad")
     _need(order, torch.int32, "order")
     _need(seg_offsets, torch.int32, "seg_offsets")
     dim = grad.shape[1]
-    if out is None:
+    if out is None and dst_table is None:
         out = torch.empty((max_unique, dim), dtype=out_dtype, device=grad.device)
-    if out.dtype not in (torch.float32, torch.float64):
+    odt = out.dtype if out is not None else out_dtype
+    if odt not in (torch.float32, torch.float64):
         raise TypeError("segreduce output must be float32 or float64")
     n_rows = grad.shape[0]
     need = lib.edl_segreduce_workspace_bytes(max_unique, n_rows, dim)
     if workspace is None or workspace.numel() < need:
         workspace = _ws(need, grad.device)
     check(lib.edl_segreduce(_ptr(grad), dim, _ptr(order), _ptr(seg_offsets), _ptr(seg_first),
-                            _ptr(n_unique), max_unique, n_rows, _ptr(out_pos), _ptr(out), int(out.dtype == torch.float64),
-                            _ptr(workspace), workspace.numel(), _stream()), "edl_segreduce")
+                            _ptr(n_unique), max_unique, n_rows, _ptr(out_pos), _ptr(out), int(odt == torch.float64),
+                            _ptr(dst_table), _ptr(workspace), workspace.numel(), _stream()), "edl_segreduce")
     return out
 
 

@@ -45,6 +45,10 @@ class CudaOps:
     def lookup(self, keys):
         return self.params.lookup(keys)
 
+    def lookup_into(self, keys, out):
+        """Gather into `out`, which may be peer-mapped memory of another GPU."""
+        K.gather_keys(self.params.slab, keys.contiguous(), self.params._layout_arg, out=out)
+
     def expand(self, rows_in, uq, part):
         return K.expand(rows_in, K.compose_index(uq.inverse, part.pos))
 
@@ -53,6 +57,10 @@ class CudaOps:
         K.segreduce(grad, uq.order, uq.seg_offsets, uq.n_unique, uq.n, seg_first=uq.seg_first,
                     out_pos=part.pos, out=g_send)
         return g_send[:n_send]
+
+    def reduce_into_peers(self, grad, uq, part, wire_dtype, dst_table):
+        K.segreduce(grad, uq.order, uq.seg_offsets, uq.n_unique, uq.n, seg_first=uq.seg_first,
+                    out_pos=part.pos, out=None, out_dtype=wire_dtype, dst_table=dst_table)
 
     def apply(self, recv_keys, g_recv):
         R = recv_keys.numel()
@@ -97,8 +105,19 @@ class ShardedSparseStep:
         recv = [int(x) for x in got.reshape(-1)]
         U = sum(send)
         recv_keys = yield ("a2av", part.keys[:U], send, recv, "fwd", "keys")
-        rows_out = self.ops.lookup(recv_keys)
-        rows_in = yield ("a2av", rows_out, recv, send, "rev", "rows")   # [U, D], partition order
+        if hasattr(self.exchange, "remote_rows") and not isinstance(self.ops, type(None)) and hasattr(self.ops, "lookup_into"):
+            # fused pack -> send: the owner's gather writes every requester's rows straight into
+            # that requester's receive buffer over NVLink; no send buffer, no copy
+            off = 0
+            for src in range(S):
+                n = recv[src]
+                if n:
+                    self.ops.lookup_into(recv_keys[off:off + n], self.exchange.remote_rows("rows", "rev", src, n))
+                off += n
+            rows_in = self.exchange.finish_round("rows", send)
+        else:
+            rows_out = self.ops.lookup(recv_keys)
+            rows_in = yield ("a2av", rows_out, recv, send, "rev", "rows")   # [U, D], partition order
         emb = self.ops.expand(rows_in, uq, part)
         self._fw = (uq, part, send, recv, recv_keys, U)
         self.last_n_unique = uq.n_unique
@@ -106,8 +125,17 @@ class ShardedSparseStep:
 
     def gen_update(self, grad: torch.Tensor) -> Generator:
         uq, part, send, recv, recv_keys, U = self._fw
-        g_send = self.ops.reduce_for_send(grad, uq, part, U, self.wire_dtype)
-        g_recv = yield ("a2av", g_send, send, recv, "fwd", "grads")   # aligned with recv_keys
+        if hasattr(self.exchange, "dst_table") and hasattr(self.ops, "reduce_into_peers"):
+            # fused reduce -> send: partial sums are stored straight into the owners' buffers
+            offs = [0]
+            for c in send:
+                offs.append(offs[-1] + c)
+            self.ops.reduce_into_peers(grad, uq, part, self.wire_dtype,
+                                       self.exchange.dst_table("grads", "fwd", offs))
+            g_recv = self.exchange.finish_round("grads", recv)
+        else:
+            g_send = self.ops.reduce_for_send(grad, uq, part, U, self.wire_dtype)
+            g_recv = yield ("a2av", g_send, send, recv, "fwd", "grads")   # aligned with recv_keys
         self.ops.apply(recv_keys, g_recv)
         return None
 

@@ -147,13 +147,17 @@ int edl_compose_index(const int32_t* index, const int32_t* map, int64_t n, int32
  * out_f64 != 0: g_out is double[.., dim], the float64 partial sums themselves -- the exact
  *               wire format of the worker -> PS gradient exchange (the owner's total is then
  *               independent of how the batch was split over workers, up to float64 rounding).
+ * dst_table (nullable, needs out_pos): fused reduce -> send.  Device int64 array
+ *   [ G, offsets[0..G], base[0..G-1] ]: output row dst(u) of group s (offsets[s] <= dst < offsets[s+1])
+ *   is stored at address base[s] + (dst - offsets[s]) rows instead of in g_out; base[s] may be another
+ *   GPU's memory mapped with edl_ipc_import, so the partial sums travel over NVLink as they are made.
  * n_unique_dev: device int32 U; max_unique: host upper bound on U; n_rows: number of gradient
  * rows (= length of `order`), which bounds the scratch for hot ids. */
 size_t edl_segreduce_workspace_bytes(int64_t max_unique, int64_t n_rows, int dim);
 int edl_segreduce(const float* grad, int dim, const int32_t* order, const int32_t* seg_offsets,
                   const int32_t* seg_first /* nullable */, const int32_t* n_unique_dev, int64_t max_unique, int64_t n_rows,
-                  const int32_t* out_pos, void* g_out, int out_f64, void* workspace,
-                  size_t workspace_bytes, edl_stream_t stream);
+                  const int32_t* out_pos, void* g_out, int out_f64, const int64_t* dst_table,
+                  void* workspace, size_t workspace_bytes, edl_stream_t stream);
 
 /* ---- A4 + A5 fused: reduce, then optimizer row update in place (lineage PS
  * push_gradients -> optimizer kernel) -------------------------------------------------------
