@@ -54,8 +54,9 @@ def parse_args():
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
     ap.add_argument("--force-sharded", action="store_true",
                     help="N=1 only: run the multi-shard code path (dedup/partition/exchange/expand) with S=1")
-    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
-                    help="N>1: all-to-all-v by NVLink peer writes (CUDA IPC) or by NCCL")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl"],
+                    help="N>1: all-to-all-v by NVLink peer writes (CUDA IPC, fused with the producing "
+                         "kernels) or by NCCL; auto = peer up to 4 GPUs, nccl above (measured)")
     ap.add_argument("--wire", default="f64", choices=["f64", "f32"],
                     help="element type of exchanged partial gradient sums (N>1)")
     return ap.parse_args()
@@ -223,6 +224,8 @@ def run_b200_arm(a):
         from easydl_b200.sharded_step import ShardedSparseStep
         from easydl_b200.exchange import PeerExchange, SingleExchange, TorchExchange
         wire_dtype = torch.float64 if a.wire == "f64" else torch.float32
+        if a.exchange == "auto":
+            a.exchange = "peer" if world <= 4 else "nccl"
         if world == 1:
             ex = SingleExchange()
         elif a.exchange == "peer":
