@@ -54,6 +54,13 @@ PROTOTYPES = {
     "edl_export_shard": (_int, [_p, _p, _p, _int, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "edl_import_shard": (_int, [_p, _p, _p, _int, _p, _p, _p, _p, _p, _p, _i64, _p]),
     "edl_scatter_rows": (_int, [_p, _int, _p, _i64, _p, _p, _p]),
+    "edl_lazy_index_bytes": (_sz, [_i64]),
+    "edl_lazy_clear": (_int, [_p, _i64, _p]),
+    "edl_lazy_gather": (_int, [_p, _i64, _p, _int, _p, _i64, _p, _p, C.c_uint64, _p, _p]),
+    "edl_lazy_insert": (_int, [_p, _i64, _p, _p, _p, _int, _i64, _p, _i64, _p, _p, C.c_uint64,
+                               C.c_float, C.c_float, _p, _p]),
+    "edl_lazy_status_ptr": (_p, [_p, _i64]),
+    "edl_lazy_dump": (_int, [_p, _i64, _p, _p, _p]),
     "edl_peer_alloc": (_int, [C.POINTER(C.c_void_p), _sz]),
     "edl_peer_free": (_int, [_p]),
     "edl_ipc_export": (_int, [_p, C.c_char_p]),

@@ -16,9 +16,11 @@ from .layout import ShardLayout
 from .parameters import ShardParameters, ShardRecords
 
 
-def gen_reshard(old: Optional[ShardParameters], new_S: int, rank: int, world: int, *, rows, dim,
-                opt, seed, device) -> Generator:
-    """Returns this rank's new ShardParameters (or None when rank >= new_S)."""
+def gen_reshard(old, new_S: int, rank: int, world: int, *, rows, dim, opt, seed, device,
+                factory=None) -> Generator:
+    """Returns this rank's new shard (or None when rank >= new_S).  `old` is any object with
+    export_records() / layout_dev (ShardParameters or LazyShardParameters); `factory(shard)` builds
+    the new shard (default: a dense ShardParameters)."""
     dev = torch.device(device)
     n_slots = opt.n_slots
     counts = torch.zeros((world, 2), dtype=torch.int64, device=dev)   # [rows to send, step]
@@ -48,7 +50,7 @@ def gen_reshard(old: Optional[ShardParameters], new_S: int, rank: int, world: in
         slots_in.append((yield ("a2av", s, send, recv)))
     if rank >= new_S:
         return None
-    new = ShardParameters(rows, dim, opt, new_S, rank, seed=seed, device=dev)
+    new = factory(rank) if factory is not None else ShardParameters(rows, dim, opt, new_S, rank, seed=seed, device=dev)
     new.import_records(ShardRecords(keys_in, rows_in, slots_in, step))
     new.step = step
     return new

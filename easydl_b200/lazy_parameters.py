@@ -1,0 +1,147 @@
+"""A PS shard that stores only the rows it has updated.
+
+Same surface as ShardParameters (lookup / apply_gradients / export_records / import_records), so
+the sharded step and the elastic re-shard run on it unchanged.  Needed when the dense slab does not
+fit: BASELINE.json configs[2] (26 x 40M rows x dim 128, Adam) is 1.6 TB dense, 200 GB per GPU on
+eight 180 GB B200s.  `max_rows` bounds the rows this shard can materialise; running out raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import torch
+
+from . import _lib
+from . import kernels as K
+from ._lib import check
+from .criteo import DEFAULT_SEED
+from .layout import ShardLayout
+from .optimizer import OptimizerSpec
+from .parameters import ShardRecords
+
+
+def _pow2_at_least(x: int) -> int:
+    p = 1
+    while p < x:
+        p <<= 1
+    return p
+
+
+class LazyShardParameters:
+    def __init__(self, rows: Sequence[int], dim: int, opt: OptimizerSpec, num_shards: int = 1,
+                 shard: int = 0, max_rows: int = 1 << 20, seed: int = DEFAULT_SEED, device="cuda:0"):
+        if dim <= 0 or dim % 4:
+            raise ValueError("dim must be a positive multiple of 4")
+        self.layout = ShardLayout(rows, num_shards, shard)
+        self.dim, self.opt, self.seed = int(dim), opt, int(seed)
+        self.device = torch.device(device)
+        self.step = 0
+        self.max_rows = int(max_rows)
+        self.layout_dev = self.layout.to_device(self.device)
+        # + 1: the spare row that absorbs writes after an overflow (reported by materialised())
+        self.slab = torch.empty((self.max_rows + 1, dim), dtype=torch.float32, device=self.device)
+        self.slots = [torch.empty((self.max_rows + 1, dim), dtype=torch.float32, device=self.device)
+                      for _ in range(opt.n_slots)]
+        self.index_capacity = _pow2_at_least(2 * self.max_rows)
+        lib = _lib.load()
+        self.index = torch.empty(lib.edl_lazy_index_bytes(self.index_capacity), dtype=torch.uint8,
+                                 device=self.device)
+        check(lib.edl_lazy_clear(self.index.data_ptr(), self.index_capacity, K._stream()), "edl_lazy_clear")
+        off = self.index_capacity * 12
+        self.status = self.index[off:off + 8].view(torch.int32)     # [rows materialised, overflow]
+        self.touched = None                                          # every stored row is a touched row
+
+    num_shards = property(lambda self: self.layout.num_shards)
+    shard = property(lambda self: self.layout.shard)
+    _layout_arg = property(lambda self: self.layout_dev)
+
+    def reset(self):
+        check(_lib.load().edl_lazy_clear(self.index.data_ptr(), self.index_capacity, K._stream()), "edl_lazy_clear")
+        self.step = 0
+
+    def materialised(self) -> int:
+        n, err = (int(x) for x in self.status.cpu())
+        if err:
+            raise RuntimeError(f"lazy shard {self.shard}: more than max_rows={self.max_rows} rows were updated")
+        return n
+
+    # ------------------------------------------------------------------ A3
+    def lookup(self, keys: torch.Tensor, *, n_dev=None, out=None) -> torch.Tensor:
+        lib = _lib.load()
+        n = keys.numel()
+        if out is None:
+            out = torch.empty((n, self.dim), dtype=torch.float32, device=self.device)
+        check(lib.edl_lazy_gather(self.index.data_ptr(), self.index_capacity, self.slab.data_ptr(), self.dim,
+                                  K._ptr(keys), n, K._ptr(n_dev), self.layout_dev.data_ptr(),
+                                  C.c_uint64(self.seed & (2 ** 64 - 1)), K._ptr(out), K._stream()),
+              "edl_lazy_gather")
+        return out
+
+    # ------------------------------------------------------------------ A4 + A5
+    def _slots_for(self, keys: torch.Tensor, n_dev=None) -> torch.Tensor:
+        lib = _lib.load()
+        n = keys.numel()
+        slots = torch.empty(max(n, 1), dtype=torch.int64, device=self.device)
+        s1 = self.slots[1] if len(self.slots) > 1 else None
+        check(lib.edl_lazy_insert(self.index.data_ptr(), self.index_capacity, self.slab.data_ptr(),
+                                  self.slots[0].data_ptr(), K._ptr(s1), self.dim, self.max_rows, K._ptr(keys), n,
+                                  K._ptr(n_dev), self.layout_dev.data_ptr(), C.c_uint64(self.seed & (2 ** 64 - 1)),
+                                  C.c_float(self.opt.slot_init(0)), C.c_float(self.opt.slot_init(1)),
+                                  slots.data_ptr(), K._stream()), "edl_lazy_insert")
+        return slots
+
+    def apply_gradients(self, uq: K.UniqueResult, grad: torch.Tensor, max_unique: Optional[int] = None,
+                        workspace=None):
+        self.step += 1
+        slots = self._slots_for(uq.uniq, uq.n_unique)
+        s1 = self.slots[1] if len(self.slots) > 1 else None
+        K.segreduce_update(self.slab, self.slots[0], s1, slots, uq.order, uq.seg_offsets, uq.n_unique,
+                           uq.n if max_unique is None else max_unique, grad, None,
+                           self.opt.params(self.step), None, workspace, seg_first=uq.seg_first)
+
+    # ------------------------------------------------------------------ A6
+    def export_records(self) -> ShardRecords:
+        lib = _lib.load()
+        n = self.materialised()
+        keys = torch.empty(max(n, 1), dtype=torch.int64, device=self.device)
+        slots = torch.empty(max(n, 1), dtype=torch.int64, device=self.device)
+        if n:
+            check(lib.edl_lazy_dump(self.index.data_ptr(), self.index_capacity, keys.data_ptr(), slots.data_ptr(),
+                                    K._stream()), "edl_lazy_dump")
+            uq = K.unique(keys[:n].contiguous(), None, self.layout.key_bits, want_inverse=False, want_counts=False)
+            order = uq.order[:n].to(torch.int64)               # ascending-key order of the slots
+            keys_sorted = uq.uniq[:n]
+            rows = K.gather_keys(self.slab, order, None)
+            sl = [K.gather_keys(s, order, None) for s in self.slots]
+        else:
+            keys_sorted = keys[:0]
+            rows = torch.empty((0, self.dim), dtype=torch.float32, device=self.device)
+            sl = [rows.clone() for _ in self.slots]
+        return ShardRecords(keys_sorted, rows, sl, self.step)
+
+    def import_records(self, rec: ShardRecords):
+        self.step = max(self.step, rec.step)
+        if len(rec) == 0:
+            return
+        # keep the records this shard owns (id mod S == shard), then insert + overwrite
+        part = K.partition_mod(rec.keys.contiguous(), self.layout_dev, self.num_shards, want_pos=False)
+        offs = [int(x) for x in part.offsets.cpu()]
+        a, b = offs[self.shard], offs[self.shard + 1]
+        if b == a:
+            return
+        keys = part.keys[a:b].contiguous()
+        perm = part.perm[a:b].contiguous()
+        slots = self._slots_for(keys)[:b - a].to(torch.int32)
+        K.scatter_rows(K.expand(rec.rows.contiguous(), perm), slots, self.slab)
+        for k, s in enumerate(self.slots):
+            K.scatter_rows(K.expand(rec.slots[k].contiguous(), perm), slots, s)
+
+    # ------------------------------------------------------------------ test helper
+    def read_rows(self, keys: torch.Tensor):
+        """(rows, slots...) of materialised keys."""
+        slots = self._slots_for(keys.contiguous())[:keys.numel()]
+        return [K.gather_keys(self.slab, slots, None)] + [K.gather_keys(s, slots, None) for s in self.slots]
+
+    def nbytes(self) -> int:
+        return self.slab.numel() * 4 * (1 + len(self.slots)) + self.index.numel()

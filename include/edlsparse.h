@@ -210,6 +210,33 @@ int edl_import_shard(float* slab, float* slot0, float* slot1, int dim, uint32_t*
 int edl_scatter_rows(const float* rows, int dim, const int32_t* pos, int64_t n,
                      const int32_t* n_dev, float* out, edl_stream_t stream);
 
+/* ---- lazily materialised rows (lineage EmbeddingTable.get lazy initialisation) --
+ * For tables that do not fit densely (configs[2]: 1.6 TB with Adam state).  A shard stores only
+ * rows that received an update, in a slab of max_rows + 1 rows (the last one is a spare that
+ * absorbs writes after an overflow), behind an open-addressing hash index
+ * fused key -> slab row.  The caller owns both: `index` is edl_lazy_index_bytes(index_capacity)
+ * bytes (index_capacity a power of two >= 2 x max_rows), cleared with edl_lazy_clear.
+ *   edl_lazy_gather : out[i] = stored row of keys[i], or the initial value init(seed, t, id)
+ *                     computed on the fly when the row was never updated (nothing is inserted).
+ *   edl_lazy_insert : for UNIQUE keys (the output of edl_unique): slots_out[i] = slab row of
+ *                     keys[i]; unseen keys claim the next free row, which is initialised
+ *                     (row = init, slot0 / slot1 = the given constants).  Feed slots_out as
+ *                     `uniq` with layout == NULL to edl_segreduce_update.
+ *   edl_lazy_status_ptr : device int32[2] = {rows materialised, overflow flag}.
+ *   edl_lazy_dump   : keys_out[s], slots_out[s] for every materialised row s (slot order). */
+size_t edl_lazy_index_bytes(int64_t index_capacity);
+int edl_lazy_clear(void* index, int64_t index_capacity, edl_stream_t stream);
+int edl_lazy_gather(const void* index, int64_t index_capacity, const float* slab, int dim,
+                    const int64_t* keys, int64_t n, const int32_t* n_dev, const int64_t* layout,
+                    uint64_t seed, float* out, edl_stream_t stream);
+int edl_lazy_insert(void* index, int64_t index_capacity, float* slab, float* slot0, float* slot1,
+                    int dim, int64_t max_rows, const int64_t* keys, int64_t n, const int32_t* n_dev,
+                    const int64_t* layout, uint64_t seed, float slot0_init, float slot1_init,
+                    int64_t* slots_out, edl_stream_t stream);
+const int32_t* edl_lazy_status_ptr(const void* index, int64_t index_capacity);
+int edl_lazy_dump(const void* index, int64_t index_capacity, int64_t* keys_out, int64_t* slots_out,
+                  edl_stream_t stream);
+
 /* ---- A7 over NVLink peer memory (replaces the worker <-> PS RPC of the lineage) ----------
  * Exchange buffers that the other ranks of the box write into directly.  Set-up: every rank
  * allocates its receive buffer (edl_peer_alloc: the one place this library allocates, because a
