@@ -381,13 +381,19 @@ def run_b200_arm(a):
             "clocks": clocks,
         }
         if phases:
+            traffic, traffic_src = None, None
+            tp = os.path.join(ROOT, "profiles", "r1f_traffic.json")
+            if os.path.exists(tp) and a.dim == 64 and a.batch == 65536 and a.optimizer == "adagrad":
+                tj = json.load(open(tp))
+                traffic, traffic_src = tj["update_dram_bytes_per_step"], tj["source"]
             t_up = phases["update_ms"] * 1e-3
             t_lk = phases["lookup_ms"] * 1e-3
             ach = update_b / t_up / 1e9
             line["roofline"] = {
-                "kernel": "k_seg_tile (segmented reduce + Adagrad row update, one launch per step)",
+                "kernel": "k_seg_direct + k_seg_chunk + k_seg_long_final (segmented reduce + row update: "
+                          "three launches per step, timed together)",
                 "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_kind": peak_kind,
+                "traffic": traffic, "traffic_source": traffic_src, "peak_kind": peak_kind,
                 "algorithmic_bytes_per_launch": update_b,
             }
             line["phases"] = dict(phases)

@@ -40,6 +40,7 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
   if (u >= U) return;
   const int s0 = seg[u], s1 = seg[u + 1];
   const int j0 = seg_first ? seg_first[u] : -1;   // first gradient row of the id, no extra hop
+  const long long tok = epi.token(uniq, u);       // key / output position: same hop as the bounds
   const int cnt = s1 - s0;
   const unsigned ROWB_G = (unsigned)D4 * R::kBytes4;
   if (kMode == 1 && cnt != 1) return;
@@ -65,7 +66,7 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
     }
     return;
   }
-  const long long row = epi.row_of(&L, uniq, u);
+  const long long row = epi.row_from(&L, tok);
   float4 p[kC], a0[kC], a1[kC];
 #pragma unroll
   for (int c = 0; c < kC; ++c) {
