@@ -11,7 +11,7 @@ constexpr int kLongThrMin = 2;  // smallest allowed threshold (sizes the scratch
 constexpr int kLongThrDefault = 16;  // segments longer than this go through the chunk path
 constexpr int kChunk = 64;     // gradient rows per chunk
 constexpr int kUnrollD = 4;    // independent row loads in flight per lane group (short path)
-constexpr int kUnrollC = 4;    // same, chunk path
+constexpr int kUnrollC = 2;    // same, chunk path
 
 struct DirectWs {
   int32_t* counters;    // [0] long segments, [1] chunks           (cleared before every call)
@@ -130,7 +130,7 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
 // here (sum + epilogue).  Longer ids leave a float64 partial row per chunk in scratch for
 // k_seg_long_final.
 template <int kG, int kC, typename GT, typename Epi>
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, 8)
 k_seg_chunk(const unsigned char* __restrict__ grad, int D4, const int32_t* __restrict__ order,
             const int32_t* __restrict__ seg, const int32_t* __restrict__ counters,
             const int32_t* __restrict__ chunk_list, int32_t* __restrict__ long_list,
@@ -297,7 +297,7 @@ int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t*
   else
     k_seg_direct<kG, kC, GT, Epi, (kC == 1 ? 8 : 4), 1><<<(unsigned)ctas, kThreads, 0, st>>>(EDL_DARGS);
 #undef EDL_DARGS
-  const int64_t gc = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_chunks * kG, kThreads), EDL_SM_COUNT * 4));
+  const int64_t gc = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_chunks * kG, kThreads), EDL_SM_COUNT * 8));
   k_seg_chunk<kG, kC, GT, Epi><<<(unsigned)gc, kThreads, 0, st>>>((const unsigned char*)grad, D4, order, seg,
                                                                   W.counters, W.chunk_list, W.long_list, W.partial,
                                                                   uniq, layout, epi);
