@@ -16,13 +16,14 @@ constexpr int kUnrollC = 2;    // same, chunk path
 struct DirectWs {
   int32_t* counters;    // [0] long segments, [1] chunks           (cleared before every call)
   int32_t* long_list;   // [max_long][4]  u, first chunk, n chunks, chunks done
-  int32_t* chunk_list;  // [max_chunks][2] long-list index, chunk index inside the segment
+  int32_t* chunk_list;  // [max_chunks][4] first position, end position, long-list index, chunk index
   double* partial;      // [max_chunks][dim]
   int64_t max_long, max_chunks;
 };
 
 // kMode: 0 every segment; 1 only ids that occur once; 2 only ids that occur more than once
-template <int kG, int kC, typename GT, typename Epi, int kMinBlocks = 4, int kUnroll = kUnrollD, int kMode = 0, int kBlock = kThreads>
+template <int kG, int kC, typename GT, typename Epi, int kMinBlocks = 4, int kUnroll = kUnrollD, int kMode = 0, int kBlock = kThreads,
+          int kBatch = 1>
 __global__ void __launch_bounds__(kBlock, kMinBlocks)
 k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __restrict__ order,
              const int32_t* __restrict__ seg, const int32_t* __restrict__ seg_first,
@@ -35,14 +36,32 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
   edl_layout_load(&L, layout);
   __syncthreads();
   const int U = *n_unique;
-  const int u = (int)(((int64_t)blockIdx.x * kBlock + threadIdx.x) / kG);
   const int gl = threadIdx.x % kG;
-  if (u >= U) return;
-  const int s0 = seg[u], s1 = seg[u + 1];
-  const int j0 = seg_first ? seg_first[u] : -1;   // first gradient row of the id, no extra hop
-  const long long tok = epi.token(uniq, u);       // key / output position: same hop as the bounds
-  const int cnt = s1 - s0;
   const unsigned ROWB_G = (unsigned)D4 * R::kBytes4;
+  // Each lane group takes kBatch ids, one CTA-width of groups apart.  The index loads (segment
+  // bounds, first row, key) of ALL of them are issued before the first id's rows are touched, so the
+  // first memory hop of ids 2..kBatch is hidden behind the work on the id before.
+  constexpr int kGroups = kBlock / kG;
+  const int ub = (int)blockIdx.x * (kGroups * kBatch) + (int)threadIdx.x / kG;
+  int s0a[kBatch], s1a[kBatch], j0a[kBatch];
+  long long toka[kBatch];
+#pragma unroll
+  for (int b = 0; b < kBatch; ++b) {
+    const int ux = ub + b * kGroups;
+    if (ux < U) {
+      s0a[b] = seg[ux]; s1a[b] = seg[ux + 1];
+      j0a[b] = seg_first ? seg_first[ux] : -1;
+      toka[b] = epi.token(uniq, ux);
+    }
+  }
+#pragma unroll
+  for (int b = 0; b < kBatch; ++b) {
+    const int u = ub + b * kGroups;
+    if (u >= U) break;
+    const int s0 = s0a[b], s1 = s1a[b], j0 = j0a[b];
+    const long long tok = toka[b];
+    [&]() {
+  const int cnt = s1 - s0;
   if (kMode == 1 && cnt != 1) return;
   if (kMode == 2 && cnt == 1) return;
   if (kMode != 1 && cnt > kLongThr) {
@@ -60,9 +79,10 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
     const unsigned gmask = kG == 32 ? 0xffffffffu : (((1u << kG) - 1u) << (lane / kG * kG));
     base = __shfl_sync(gmask, base, lane / kG * kG);
     li = __shfl_sync(gmask, li, lane / kG * kG);
-    for (int c = gl; c < nch; c += kG) {
-      chunk_list[(base + c) * 2 + 0] = li;
-      chunk_list[(base + c) * 2 + 1] = c;
+    for (int c = gl; c < nch; c += kG) {   // begin / end stored here: the chunk kernel needs one hop less
+      const int b = s0 + c * kChunk;
+      int4 ent = make_int4(b, min(s1, b + kChunk), li, c);
+      ((int4*)chunk_list)[base + c] = ent;
     }
     return;
   }
@@ -124,6 +144,8 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
     }
   }
   if (gl == 0) epi.touch(row);
+    }();
+  }
 }
 
 // One lane group per chunk (<= kChunk rows) of a hot id.  An id that fits one chunk is finished
@@ -148,10 +170,9 @@ k_seg_chunk(const unsigned char* __restrict__ grad, int D4, const int32_t* __res
   const unsigned ROWB_G = (unsigned)D4 * R::kBytes4;
   const int D = D4 * 4;
   for (int ci = (int)(((int64_t)blockIdx.x * kThreads + threadIdx.x) / kG); ci < n_chunks; ci += groups) {
-    const int li = chunk_list[ci * 2], c0 = chunk_list[ci * 2 + 1];
-    const int u = long_list[li * 4], base = long_list[li * 4 + 1], nch = long_list[li * 4 + 2];
-    const int b = seg[u] + c0 * kChunk;
-    const int e = min(seg[u + 1], b + kChunk);
+    const int4 ent = ((const int4*)chunk_list)[ci];
+    const int b = ent.x, e = ent.y, li = ent.z;
+    const int u = long_list[li * 4], nch = long_list[li * 4 + 2];   // needed after the sum only
     double acc[kC][4];
 #pragma unroll
     for (int c = 0; c < kC; ++c) acc[c][0] = acc[c][1] = acc[c][2] = acc[c][3] = 0.0;
@@ -287,6 +308,8 @@ int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t*
   // 8 CTAs x 256 threads per SM (<= 32 registers) and one row in flight per lane group: measured
   // faster than fewer, fatter threads (profiles/r1_direct_variants.md) -- the loads that hide HBM
   // latency come from occupancy, not from unrolling.
+  static int batch = -1;
+  if (batch < 0) { const char* e = getenv("EDL_DIRECT_BATCH"); batch = e ? atoi(e) : 2; }
   static int blk = -1;
   if (blk < 0) { const char* e = getenv("EDL_DIRECT_BLOCK"); blk = e ? atoi(e) : 256; }
 #define EDL_DARGS (const unsigned char*)grad, D4, order, seg, seg_first, n_unique, uniq, layout, epi, W.counters, W.long_list, W.chunk_list, long_thr
@@ -294,6 +317,18 @@ int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t*
     k_seg_direct<kG, kC, GT, Epi, 32, 1, 0, 64><<<(unsigned)edl_cdiv(max_unique * kG, 64), 64, 0, st>>>(EDL_DARGS);
   else if (kC == 1 && blk == 128)
     k_seg_direct<kG, kC, GT, Epi, 16, 1, 0, 128><<<(unsigned)edl_cdiv(max_unique * kG, 128), 128, 0, st>>>(EDL_DARGS);
+  else if (kC == 1 && batch == 2)
+    k_seg_direct<kG, kC, GT, Epi, 8, 1, 0, kThreads, 2><<<(unsigned)edl_cdiv(ctas, 2), kThreads, 0, st>>>(EDL_DARGS);
+  else if (kC == 1 && batch == 4)
+    k_seg_direct<kG, kC, GT, Epi, 8, 1, 0, kThreads, 4><<<(unsigned)edl_cdiv(ctas, 4), kThreads, 0, st>>>(EDL_DARGS);
+  else if (kC == 1 && batch == 22)
+    k_seg_direct<kG, kC, GT, Epi, 7, 1, 0, kThreads, 2><<<(unsigned)edl_cdiv(ctas, 2), kThreads, 0, st>>>(EDL_DARGS);
+  else if (kC == 1 && batch == 23)
+    k_seg_direct<kG, kC, GT, Epi, 6, 1, 0, kThreads, 3><<<(unsigned)edl_cdiv(ctas, 3), kThreads, 0, st>>>(EDL_DARGS);
+  else if (kC == 1 && batch == 24)
+    k_seg_direct<kG, kC, GT, Epi, 6, 1, 0, kThreads, 4><<<(unsigned)edl_cdiv(ctas, 4), kThreads, 0, st>>>(EDL_DARGS);
+  else if (kC == 1 && batch == 25)
+    k_seg_direct<kG, kC, GT, Epi, 6, 1, 0, kThreads, 2><<<(unsigned)edl_cdiv(ctas, 2), kThreads, 0, st>>>(EDL_DARGS);
   else
     k_seg_direct<kG, kC, GT, Epi, (kC == 1 ? 8 : 4), 1><<<(unsigned)ctas, kThreads, 0, st>>>(EDL_DARGS);
 #undef EDL_DARGS

@@ -32,7 +32,7 @@ Ws carve_ws(void* ws, int64_t n_rows, int dim) {
   w.direct.max_long = n / (kLongThrMin + 1) + 1;
   w.direct.max_chunks = n / kChunk + w.direct.max_long + 1;
   w.direct.long_list = (int32_t*)(p + off); off = edl_align_up(off + (size_t)w.direct.max_long * 4 * 4, 256);
-  w.direct.chunk_list = (int32_t*)(p + off); off = edl_align_up(off + (size_t)w.direct.max_chunks * 2 * 4, 256);
+  w.direct.chunk_list = (int32_t*)(p + off); off = edl_align_up(off + (size_t)w.direct.max_chunks * 4 * 4, 256);
   w.direct.partial = (double*)(p + off); off = edl_align_up(off + (size_t)w.direct.max_chunks * dim * 8, 256);
   w.tile.bytes = off;
   w.bytes = off;
