@@ -382,7 +382,7 @@ def run_b200_arm(a):
         }
         if phases:
             traffic, traffic_src = None, None
-            tp = os.path.join(ROOT, "profiles", "r1f_traffic.json")
+            tp = os.path.join(ROOT, "profiles", "traffic.json")
             if os.path.exists(tp) and a.dim == 64 and a.batch == 65536 and a.optimizer == "adagrad":
                 tj = json.load(open(tp))
                 traffic, traffic_src = tj["update_dram_bytes_per_step"], tj["source"]
