@@ -13,13 +13,6 @@ constexpr int kChunk = 64;     // gradient rows per chunk
 constexpr int kUnrollD = 4;    // independent row loads in flight per lane group (short path)
 constexpr int kUnrollC = 2;    // same, chunk path
 
-struct DirectWs {
-  int32_t* counters;    // [0] long segments, [1] chunks           (cleared before every call)
-  int32_t* long_list;   // [max_long][4]  u, first chunk, n chunks, chunks done
-  int32_t* chunk_list;  // [max_chunks][4] first position, end position, long-list index, chunk index
-  double* partial;      // [max_chunks][dim]
-  int64_t max_long, max_chunks;
-};
 
 // kMode: 0 every segment; 1 only ids that occur once; 2 only ids that occur more than once
 template <int kG, int kC, typename GT, typename Epi, int kMinBlocks = 4, int kUnroll = kUnrollD, int kMode = 0, int kBlock = kThreads,
@@ -308,27 +301,11 @@ int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t*
   // 8 CTAs x 256 threads per SM (<= 32 registers) and one row in flight per lane group: measured
   // faster than fewer, fatter threads (profiles/r1_direct_variants.md) -- the loads that hide HBM
   // latency come from occupancy, not from unrolling.
-  static int batch = -1;
+  static int batch = -1;   // ids per lane group (EDL_DIRECT_BATCH=1 switches the index prefetch off)
   if (batch < 0) { const char* e = getenv("EDL_DIRECT_BATCH"); batch = e ? atoi(e) : 2; }
-  static int blk = -1;
-  if (blk < 0) { const char* e = getenv("EDL_DIRECT_BLOCK"); blk = e ? atoi(e) : 256; }
 #define EDL_DARGS (const unsigned char*)grad, D4, order, seg, seg_first, n_unique, uniq, layout, epi, W.counters, W.long_list, W.chunk_list, long_thr
-  if (kC == 1 && blk == 64)
-    k_seg_direct<kG, kC, GT, Epi, 32, 1, 0, 64><<<(unsigned)edl_cdiv(max_unique * kG, 64), 64, 0, st>>>(EDL_DARGS);
-  else if (kC == 1 && blk == 128)
-    k_seg_direct<kG, kC, GT, Epi, 16, 1, 0, 128><<<(unsigned)edl_cdiv(max_unique * kG, 128), 128, 0, st>>>(EDL_DARGS);
-  else if (kC == 1 && batch == 2)
+  if (kC == 1 && batch == 2)
     k_seg_direct<kG, kC, GT, Epi, 8, 1, 0, kThreads, 2><<<(unsigned)edl_cdiv(ctas, 2), kThreads, 0, st>>>(EDL_DARGS);
-  else if (kC == 1 && batch == 4)
-    k_seg_direct<kG, kC, GT, Epi, 8, 1, 0, kThreads, 4><<<(unsigned)edl_cdiv(ctas, 4), kThreads, 0, st>>>(EDL_DARGS);
-  else if (kC == 1 && batch == 22)
-    k_seg_direct<kG, kC, GT, Epi, 7, 1, 0, kThreads, 2><<<(unsigned)edl_cdiv(ctas, 2), kThreads, 0, st>>>(EDL_DARGS);
-  else if (kC == 1 && batch == 23)
-    k_seg_direct<kG, kC, GT, Epi, 6, 1, 0, kThreads, 3><<<(unsigned)edl_cdiv(ctas, 3), kThreads, 0, st>>>(EDL_DARGS);
-  else if (kC == 1 && batch == 24)
-    k_seg_direct<kG, kC, GT, Epi, 6, 1, 0, kThreads, 4><<<(unsigned)edl_cdiv(ctas, 4), kThreads, 0, st>>>(EDL_DARGS);
-  else if (kC == 1 && batch == 25)
-    k_seg_direct<kG, kC, GT, Epi, 6, 1, 0, kThreads, 2><<<(unsigned)edl_cdiv(ctas, 2), kThreads, 0, st>>>(EDL_DARGS);
   else
     k_seg_direct<kG, kC, GT, Epi, (kC == 1 ? 8 : 4), 1><<<(unsigned)ctas, kThreads, 0, st>>>(EDL_DARGS);
 #undef EDL_DARGS
@@ -341,6 +318,18 @@ int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t*
                                                                  layout, epi);
   EDL_LAUNCH_CHECK("k_seg_direct / k_seg_chunk");
   return EDL_OK;
+}
+
+// type-erased entry of this kernel family (update.cu)
+inline int seg_run_direct(const SegCall& c, const DirectWs& W) {
+  return seg_with_epi(c, [&](auto gt, auto epi) {
+    using GT = decltype(gt);
+    using Epi = decltype(epi);
+    return seg_with_dim(c.dim, [&](auto G, auto C) {
+      return launch_direct<decltype(G)::value, decltype(C)::value, GT, Epi>(
+          c.grad, c.dim / 4, c.order, c.seg, c.seg_first, c.n_unique, c.max_unique, c.uniq, c.layout, epi, W, c.st);
+    });
+  });
 }
 
 }  // namespace

@@ -1,6 +1,7 @@
-// k_seg_tile: shared-memory staged, position-balanced segmented reduce + optimizer (see the design
-// notes at the top of update.cu).  Included by update.cu only.
-#pragma once
+// k_seg_tile: shared-memory staged, position-balanced segmented reduce + optimizer -- the alternative
+// kernel family (EDL_SEG_IMPL=tile).  Persistent CTAs over slices of the SORTED positions, rows copied
+// asynchronously (LDGSTS; TMA bulk with -DEDL_TILE_BULK) into a 3-stage shared-memory ring, index
+// metadata prefetched one window ahead, float64 carries across stages and CTAs.  Own translation unit.
 #include "seg_common.cuh"
 
 namespace {
@@ -484,9 +485,6 @@ k_seg_tile(TileParams P, Epi epi) {
 }
 
 // ------------------------------------------------------------------ host side
-constexpr int kMaxGrid = EDL_SM_COUNT * 4;
-
-struct SegWs { double* carry_h; double* carry_t; int32_t* flags; unsigned* ticket; size_t zero_bytes; size_t bytes; };
 struct StageCfg { int rows, segs, ctas_per_sm; size_t smem; };
 
 // bytes before the long-run partial buffer ([NG][dim] float64 = kThreads * 4 * 8 bytes per
@@ -539,12 +537,19 @@ int launch_tile(const void* grad, int D4, const int32_t* order, const int32_t* s
     const char* d = getenv("EDL_SEG_DEBUG");
     s_debug = d ? atoi(d) : 0;
   }
+#ifdef EDL_TILE_BULK
   auto kern = s_bulk ? k_seg_tile<kG, kC, GT, Epi, true> : k_seg_tile<kG, kC, GT, Epi, false>;
+#else
+  (void)s_bulk;
+  auto kern = k_seg_tile<kG, kC, GT, Epi, false>;
+#endif
   static int attr_smem[64] = {0};  // per device: opt in to > 48 KB dynamic shared memory once
   int dev = 0;
   EDL_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || attr_smem[dev] < (int)cfg.smem) {
+#ifdef EDL_TILE_BULK
     EDL_CUDA(cudaFuncSetAttribute(k_seg_tile<kG, kC, GT, Epi, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem));
+#endif
     EDL_CUDA(cudaFuncSetAttribute(k_seg_tile<kG, kC, GT, Epi, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.smem));
     if (dev >= 0 && dev < 64) attr_smem[dev] = (int)cfg.smem;
   }
@@ -561,3 +566,15 @@ int launch_tile(const void* grad, int D4, const int32_t* order, const int32_t* s
 }
 
 }  // namespace
+
+// type-erased entry of this kernel family (declared in update.cu)
+int edl_seg_run_tile(const SegCall& c, const SegWs& W) {
+  return seg_with_epi(c, [&](auto gt, auto epi) {
+    using GT = decltype(gt);
+    using Epi = decltype(epi);
+    return seg_with_dim(c.dim, [&](auto G, auto C) {
+      return launch_tile<decltype(G)::value, decltype(C)::value, GT, Epi>(
+          c.grad, c.dim / 4, c.order, c.seg, c.n_unique, c.max_unique, c.uniq, c.layout, epi, W, c.st);
+    });
+  });
+}

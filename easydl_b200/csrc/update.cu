@@ -7,11 +7,12 @@
 // to FMA and the result matches the NumPy oracle op for op).
 //
 //   seg_direct.cuh  register path: one lane group per id, hot ids cut into chunks (default)
-//   seg_tile.cuh    shared-memory staged path: persistent CTAs over the sorted positions,
+//   seg_tile.cu     shared-memory staged path: persistent CTAs over the sorted positions,
 //                   asynchronous row copies into a 3-stage ring (EDL_SEG_IMPL=tile)
 #include "seg_common.cuh"
 #include "seg_direct.cuh"
-#include "seg_tile.cuh"
+
+int edl_seg_run_tile(const SegCall& c, const SegWs& W);   // seg_tile.cu
 
 namespace {
 
@@ -48,25 +49,9 @@ bool use_tile_impl() {
   return v == 1;
 }
 
-template <typename GT, typename Epi>
-int dispatch_dim(const void* grad, int dim, const int32_t* order, const int32_t* seg,
-                 const int32_t* seg_first, const int32_t* n_unique, int64_t max_unique, const int64_t* uniq,
-                 const int64_t* layout, Epi epi, const Ws& W, cudaStream_t st) {
-  const int D4 = dim / 4;
-  EDL_CUDA(cudaMemsetAsync(W.tile.flags, 0, W.zero_bytes, st));
-  const bool tile = use_tile_impl();
-#define EDL_GO(G, C)                                                                                          \
-  return tile ? launch_tile<G, C, GT, Epi>(grad, D4, order, seg, n_unique, max_unique, uniq, layout, epi, W.tile, st) \
-              : launch_direct<G, C, GT, Epi>(grad, D4, order, seg, seg_first, n_unique, max_unique, uniq, layout, epi, W.direct, st)
-  if (D4 <= 4) EDL_GO(4, 1);
-  if (D4 <= 8) EDL_GO(8, 1);
-  if (D4 <= 16) EDL_GO(16, 1);
-  if (D4 <= 32) EDL_GO(32, 1);
-  if (D4 <= 64) EDL_GO(32, 2);
-  if (D4 <= 128) EDL_GO(32, 4);
-#undef EDL_GO
-  edl_set_error("segreduce: dim=%d above the supported maximum 512", dim);
-  return EDL_ELIMIT;
+int run_call(const SegCall& c, const Ws& W) {
+  EDL_CUDA(cudaMemsetAsync(W.tile.flags, 0, W.zero_bytes, c.st));
+  return use_tile_impl() ? edl_seg_run_tile(c, W.tile) : seg_run_direct(c, W.direct);
 }
 
 int check_common(const char* who, const void* grad, int dim, const int32_t* order,
@@ -104,15 +89,12 @@ extern "C" int edl_segreduce(const float* grad, int dim, const int32_t* order,
   EDL_REQUIRE(dst_table || (g_out && (((uintptr_t)g_out) & 15) == 0), EDL_EINVAL,
               "edl_segreduce: g_out null or misaligned (and no dst_table)");
   EDL_REQUIRE(!dst_table || out_pos, EDL_EINVAL, "edl_segreduce: dst_table needs out_pos");
-  cudaStream_t st = (cudaStream_t)stream;
-  if (out_f64) {
-    EpiWrite64 epi{(double*)g_out, out_pos, dst_table};
-    return dispatch_dim<float, EpiWrite64>(grad, dim, order, seg_offsets, seg_first, n_unique_dev, max_unique, nullptr,
-                                           nullptr, epi, W, st);
-  }
-  EpiWrite epi{(float4*)g_out, out_pos, dst_table};
-  return dispatch_dim<float, EpiWrite>(grad, dim, order, seg_offsets, seg_first, n_unique_dev, max_unique, nullptr,
-                                       nullptr, epi, W, st);
+  SegCall c{};
+  c.grad = grad; c.dim = dim; c.grad_f64 = 0; c.order = order; c.seg = seg_offsets; c.seg_first = seg_first;
+  c.n_unique = n_unique_dev; c.max_unique = max_unique; c.uniq = nullptr; c.layout = nullptr;
+  c.epi_kind = out_f64 ? 1 : 0; c.g_out = g_out; c.out_pos = out_pos; c.dst_table = dst_table;
+  c.st = (cudaStream_t)stream;
+  return run_call(c, W);
 }
 
 extern "C" int edl_segreduce_update(float* slab, float* slot0, float* slot1, int dim,
@@ -136,18 +118,14 @@ extern "C" int edl_segreduce_update(float* slab, float* slot0, float* slot1, int
   o.lr = opt->lr; o.eps = opt->eps; o.b1 = opt->beta1; o.b2 = opt->beta2;
   o.omb1 = 1.0f - opt->beta1;  // fp32 subtraction, as the oracle does
   o.omb2 = 1.0f - opt->beta2;
-  cudaStream_t st = (cudaStream_t)stream;
-  if (opt->kind == EDL_OPT_ADAGRAD) {
-    EpiAdagrad epi{(float4*)slab, (float4*)slot0, touched, o};
-    return grad_f64 ? dispatch_dim<double, EpiAdagrad>(grad, dim, order, seg_offsets, seg_first, n_unique_dev, max_unique, uniq, layout, epi, W, st)
-                    : dispatch_dim<float, EpiAdagrad>(grad, dim, order, seg_offsets, seg_first, n_unique_dev, max_unique, uniq, layout, epi, W, st);
-  }
-  if (opt->kind == EDL_OPT_ADAM) {
-    EDL_REQUIRE(slot1, EDL_EINVAL, "edl_segreduce_update: Adam needs slot1 (v)");
-    EpiAdam epi{(float4*)slab, (float4*)slot0, (float4*)slot1, touched, o};
-    return grad_f64 ? dispatch_dim<double, EpiAdam>(grad, dim, order, seg_offsets, seg_first, n_unique_dev, max_unique, uniq, layout, epi, W, st)
-                    : dispatch_dim<float, EpiAdam>(grad, dim, order, seg_offsets, seg_first, n_unique_dev, max_unique, uniq, layout, epi, W, st);
-  }
-  edl_set_error("edl_segreduce_update: unknown optimizer kind %d", opt->kind);
-  return EDL_EINVAL;
+  EDL_REQUIRE(opt->kind == EDL_OPT_ADAGRAD || opt->kind == EDL_OPT_ADAM, EDL_EINVAL,
+              "edl_segreduce_update: unknown optimizer kind %d", opt->kind);
+  EDL_REQUIRE(opt->kind != EDL_OPT_ADAM || slot1, EDL_EINVAL, "edl_segreduce_update: Adam needs slot1 (v)");
+  SegCall c{};
+  c.grad = grad; c.dim = dim; c.grad_f64 = grad_f64; c.order = order; c.seg = seg_offsets; c.seg_first = seg_first;
+  c.n_unique = n_unique_dev; c.max_unique = max_unique; c.uniq = uniq; c.layout = layout;
+  c.epi_kind = opt->kind == EDL_OPT_ADAGRAD ? 2 : 3;
+  c.slab = slab; c.slot0 = slot0; c.slot1 = slot1; c.touched = touched; c.opt = o;
+  c.st = (cudaStream_t)stream;
+  return run_call(c, W);
 }
