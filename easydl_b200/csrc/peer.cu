@@ -64,7 +64,7 @@ __global__ void k_signal_wait(long long* const* peer_flags, volatile long long* 
   long long* dst = peer_flags[r] + me;
   asm volatile("st.release.sys.global.s64 [%0], %1;" ::"l"(dst), "l"(value) : "memory");
   long long seen = 0;
-  for (long long spins = 0; spins < (1ll << 31); ++spins) {
+  for (long long spins = 0; spins < (1ll << 27); ++spins) {   // ~2 minutes of polling
     asm volatile("ld.acquire.sys.global.s64 %0, [%1];" : "=l"(seen) : "l"(own_flags + r) : "memory");
     if (seen >= value) break;
   }

@@ -144,8 +144,9 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
 // One lane group per chunk (<= kChunk rows) of a hot id.  An id that fits one chunk is finished
 // here (sum + epilogue).  Longer ids leave a float64 partial row per chunk in scratch for
 // k_seg_long_final.
+// occupancy target by row width: 32 registers only pay off while one float4 per lane is live
 template <int kG, int kC, typename GT, typename Epi>
-__global__ void __launch_bounds__(kThreads, 8)
+__global__ void __launch_bounds__(kThreads, (kC == 1 ? 8 : (kC == 2 ? 4 : 2)))
 k_seg_chunk(const unsigned char* __restrict__ grad, int D4, const int32_t* __restrict__ order,
             const int32_t* __restrict__ seg, const int32_t* __restrict__ counters,
             const int32_t* __restrict__ chunk_list, int32_t* __restrict__ long_list,
@@ -304,10 +305,14 @@ int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t*
   static int batch = -1;   // ids per lane group (EDL_DIRECT_BATCH=1 switches the index prefetch off)
   if (batch < 0) { const char* e = getenv("EDL_DIRECT_BATCH"); batch = e ? atoi(e) : 2; }
 #define EDL_DARGS (const unsigned char*)grad, D4, order, seg, seg_first, n_unique, uniq, layout, epi, W.counters, W.long_list, W.chunk_list, long_thr
-  if (kC == 1 && batch == 2)
-    k_seg_direct<kG, kC, GT, Epi, 8, 1, 0, kThreads, 2><<<(unsigned)edl_cdiv(ctas, 2), kThreads, 0, st>>>(EDL_DARGS);
-  else
-    k_seg_direct<kG, kC, GT, Epi, (kC == 1 ? 8 : 4), 1><<<(unsigned)ctas, kThreads, 0, st>>>(EDL_DARGS);
+  if constexpr (kC == 1) {
+    if (batch == 2)
+      k_seg_direct<kG, kC, GT, Epi, 8, 1, 0, kThreads, 2><<<(unsigned)edl_cdiv(ctas, 2), kThreads, 0, st>>>(EDL_DARGS);
+    else
+      k_seg_direct<kG, kC, GT, Epi, 8, 1><<<(unsigned)ctas, kThreads, 0, st>>>(EDL_DARGS);
+  } else {
+    k_seg_direct<kG, kC, GT, Epi, (kC == 2 ? 4 : 2), 1><<<(unsigned)ctas, kThreads, 0, st>>>(EDL_DARGS);
+  }
 #undef EDL_DARGS
   const int64_t gc = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_chunks * kG, kThreads), EDL_SM_COUNT * 8));
   k_seg_chunk<kG, kC, GT, Epi><<<(unsigned)gc, kThreads, 0, st>>>((const unsigned char*)grad, D4, order, seg,
