@@ -92,7 +92,7 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
     for (int c = 0; c < kC; ++c) {
       const int col = gl + c * kG;
       if (col < D4) {
-        typename R::V v = R::ld(grad + (size_t)j * ROWB_G, col);
+        typename R::V v = R::ldg(grad + (size_t)j * ROWB_G, col);
         double s[4] = {0.0, 0.0, 0.0, 0.0};
         if (Epi::kOutF64) R::add(s, v);
         epi.apply(row, D4, col, R::f32(v), s, p[c], a0[c], a1[c]);
@@ -111,7 +111,7 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
 #pragma unroll
           for (int c = 0; c < kC; ++c) {
             const int col = gl + c * kG;
-            if (col < D4) v[k][c] = R::ld(grad + (size_t)j * ROWB_G, col);
+            if (col < D4) v[k][c] = R::ldg(grad + (size_t)j * ROWB_G, col);
           }
         }
       }
@@ -179,7 +179,7 @@ k_seg_chunk(const unsigned char* __restrict__ grad, int D4, const int32_t* __res
 #pragma unroll
           for (int c = 0; c < kC; ++c) {
             const int col = gl + c * kG;
-            if (col < D4) v[k][c] = R::ld(grad + (size_t)j * ROWB_G, col);
+            if (col < D4) v[k][c] = R::ldg(grad + (size_t)j * ROWB_G, col);
           }
         }
       }
