@@ -58,7 +58,9 @@ def parse_args():
                     help="N>1: all-to-all-v by NVLink peer writes (CUDA IPC, fused with the producing "
                          "kernels) or by NCCL; auto = peer up to 4 GPUs, nccl above (measured)")
     ap.add_argument("--wire", default="f64", choices=["f64", "f32"],
-                    help="element type of exchanged partial gradient sums (N>1)")
+                    help="element type of exchanged partial gradient sums (N>1).  f64 is the parity-validated "
+                         "default; f32 halves the gradient bytes but breaks the 1e-6 tolerance for very hot ids "
+                         "(8 workers, tests/test_gpu_sharded.py) and for Adam")
     return ap.parse_args()
 
 

@@ -29,13 +29,13 @@ def _make(cuda, rows, dim, S, opt_name):
     return params, po, oo
 
 
-def _train(cuda, params, oshards, rows, dim, batch, steps, alpha, step0=0, fresh=None):
+def _train(cuda, params, oshards, rows, dim, batch, steps, alpha, step0=0, fresh=None, wire=torch.float64):
     from easydl_b200.exchange import run_lockstep
     from easydl_b200.sharded_step import ShardedSparseStep
     S = len(params)
     fresh = (step0 == 0) if fresh is None else fresh
     bases = O.key_bases(rows)
-    st = [ShardedSparseStep(p, batch) for p in params]
+    st = [ShardedSparseStep(p, batch, wire_dtype=wire) for p in params]
     for k in range(steps):
         kw, gw, gens = [], [], []
         for r in range(S):
@@ -74,6 +74,35 @@ def test_sharded_step_matches_global_oracle(cuda, S, opt):
     osh = [O.OracleShard(rows, dim, oo, S, s) for s in range(S)]
     _train(cuda, params, osh, rows, dim, 512, 3, 1.05)
     _compare_state(cuda, params, osh, oo.n_slots)
+
+
+@pytest.mark.parametrize("S", [2, 8])
+def test_fp32_gradient_wire_error_bound(cuda, S):
+    """The optional fp32 wire (per-worker partial sums rounded to fp32 before the exchange, half the
+    gradient bytes) is NOT inside the 1e-6 tolerance for ids that every worker hits hundreds of times
+    (tables of 11 and 6 rows here): measured up to ~2e-6 relative with 8 workers.  This test pins the
+    looser bound it does keep (1e-5), which is why float64 is the default wire."""
+    rows, dim = [5000, 301, 70001, 11, 6], 64
+    params, po, oo = _make(cuda, rows, dim, S, "adagrad")
+    osh = [O.OracleShard(rows, dim, oo, S, s) for s in range(S)]
+    from easydl_b200.exchange import run_lockstep
+    from easydl_b200.sharded_step import ShardedSparseStep
+    bases = O.key_bases(rows)
+    st = [ShardedSparseStep(p, 1024, wire_dtype=torch.float32) for p in params]
+    for k in range(3):
+        kw, gw, gens = [], [], []
+        for r in range(S):
+            _, ids, _ = O.criteo_batch(rows, 1024, 1.2, step=k * 8 + r)
+            g = O.synthetic_grad(ids.size, dim, step=k * 8 + r)
+            kw.append(O.fuse_keys(ids, bases)); gw.append(g)
+            gens.append(st[r].gen_step(dev(ids, cuda), dev(g, cuda)))
+        run_lockstep(gens)
+        O.sharded_step(osh, kw, gw)
+    for p, o in zip(params, osh):
+        rec = p.export_records().cpu()
+        assert np.array_equal(rec.keys.numpy(), o.keys)
+        np.testing.assert_allclose(rec.rows.numpy(), o.w, rtol=1e-5, atol=1e-8)
+        np.testing.assert_allclose(rec.slots[0].numpy(), o.slots[0], rtol=1e-5, atol=1e-8)
 
 
 def test_cfg3_shape_reduced_rows(cuda):
