@@ -392,8 +392,8 @@ def run_b200_arm(a):
             t_lk = phases["lookup_ms"] * 1e-3
             ach = update_b / t_up / 1e9
             line["roofline"] = {
-                "kernel": "k_seg_direct + k_seg_chunk + k_seg_long_final (segmented reduce + row update: "
-                          "three launches per step, timed together)",
+                "kernel": "k_seg_classify + k_seg_direct || (k_seg_chunk + k_seg_long_final) (segmented reduce + "
+                          "row update: four launches per step, hot-id kernels on a forked branch, timed together)",
                 "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": traffic, "traffic_source": traffic_src, "peak_kind": peak_kind,
                 "algorithmic_bytes_per_launch": update_b,

@@ -3,6 +3,7 @@
 // per SM.  Hot ids (more than kLongThr gradient rows) are cut into kChunk-row chunks that are
 // summed by separate lane groups (k_seg_chunk) -- balanced under any Zipf skew and deterministic.  Included by update.cu.
 #pragma once
+#include <mutex>
 #include "seg_common.cuh"
 
 namespace {
@@ -12,6 +13,7 @@ constexpr int kLongThrDefault = 16;  // segments longer than this go through the
 constexpr int kChunk = 64;     // gradient rows per chunk
 constexpr int kUnrollD = 4;    // independent row loads in flight per lane group (short path)
 constexpr int kUnrollC = 2;    // same, chunk path
+constexpr int kForkDefault = 1; // EDL_SEG_FORK default
 
 
 // kMode: 0 every segment; 1 only ids that occur once; 2 only ids that occur more than once
@@ -58,6 +60,7 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
   if (kMode == 1 && cnt != 1) return;
   if (kMode == 2 && cnt == 1) return;
   if (kMode != 1 && cnt > kLongThr) {
+    if (!counters) return;   // k_seg_classify listed the hot ids already (forked launch)
     // hot id: register its chunks (one lane claims the slots, the group fills them)
     const int nch = (cnt + kChunk - 1) / kChunk;
     int base = 0, li = 0;
@@ -139,6 +142,49 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
   if (gl == 0) epi.touch(row);
     }();
   }
+}
+
+// Forked launch only: the hot-id lists made ahead of k_seg_direct (one thread per id), so that the
+// chunk kernels do not have to wait for it.  Same list layout as the in-kernel registration.
+__global__ void __launch_bounds__(kThreads)
+k_seg_classify(const int32_t* __restrict__ seg, const int32_t* __restrict__ n_unique,
+               int32_t* __restrict__ counters, int32_t* __restrict__ long_list,
+               int32_t* __restrict__ chunk_list, int kLongThr) {
+  const int U = *n_unique;
+  const int u = (int)blockIdx.x * kThreads + (int)threadIdx.x;
+  if (u >= U) return;
+  const int s0 = seg[u], s1 = seg[u + 1];
+  if (s1 - s0 <= kLongThr) return;
+  const int nch = (s1 - s0 + kChunk - 1) / kChunk;
+  const int base = atomicAdd(&counters[1], nch);
+  const int li = atomicAdd(&counters[0], 1);
+  ((int4*)long_list)[li] = make_int4(u, base, nch, 0);
+  for (int c = 0; c < nch; ++c) {
+    const int b = s0 + c * kChunk;
+    ((int4*)chunk_list)[base + c] = make_int4(b, min(s1, b + kChunk), li, c);
+  }
+}
+
+// Helper stream of the forked launch, one per device, made on the first call on that device (which
+// therefore must not be inside a stream capture).  The mutex keeps one call's record/wait pairs
+// on the shared events together when several host threads drive one device.
+struct ForkRes { cudaStream_t side; cudaEvent_t fork, join; bool ready; };
+inline int fork_res(ForkRes** out) {
+  static ForkRes res[64];
+  int dev = 0;
+  EDL_CUDA(cudaGetDevice(&dev));
+  EDL_REQUIRE(dev >= 0 && dev < 64, EDL_ELIMIT, "segreduce: device index %d out of range", dev);
+  ForkRes& r = res[dev];
+  if (!r.ready) {
+    int lo = 0, hi = 0;
+    EDL_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    EDL_CUDA(cudaStreamCreateWithPriority(&r.side, cudaStreamNonBlocking, hi));
+    EDL_CUDA(cudaEventCreateWithFlags(&r.fork, cudaEventDisableTiming));
+    EDL_CUDA(cudaEventCreateWithFlags(&r.join, cudaEventDisableTiming));
+    r.ready = true;
+  }
+  *out = &r;
+  return EDL_OK;
 }
 
 // One lane group per chunk (<= kChunk rows) of a hot id.  An id that fits one chunk is finished
@@ -304,7 +350,37 @@ int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t*
   // latency come from occupancy, not from unrolling.
   static int batch = -1;   // ids per lane group (EDL_DIRECT_BATCH=1 switches the index prefetch off)
   if (batch < 0) { const char* e = getenv("EDL_DIRECT_BATCH"); batch = e ? atoi(e) : 2; }
-#define EDL_DARGS (const unsigned char*)grad, D4, order, seg, seg_first, n_unique, uniq, layout, epi, W.counters, W.long_list, W.chunk_list, long_thr
+  // EDL_SEG_FORK=1: hot ids are listed first and their chunk kernels run on a helper stream beside
+  // k_seg_direct (their latency tail hides under it); 0: the three kernels in a row on `st`.
+  static int fork = -1;
+  if (fork < 0) { const char* e = getenv("EDL_SEG_FORK"); fork = e ? atoi(e) : kForkDefault; }
+  static std::mutex fork_mu;
+  std::unique_lock<std::mutex> lock(fork_mu, std::defer_lock);
+  ForkRes* F = nullptr;
+  cudaStream_t st_hot = st;
+  int32_t* reg_counters = W.counters;
+  if (fork) {
+    lock.lock();
+    int rc = fork_res(&F);
+    if (rc) return rc;
+    k_seg_classify<<<(unsigned)edl_cdiv(max_unique, kThreads), kThreads, 0, st>>>(seg, n_unique, W.counters, W.long_list,
+                                                                                 W.chunk_list, long_thr);
+    EDL_CUDA(cudaEventRecord(F->fork, st));
+    EDL_CUDA(cudaStreamWaitEvent(F->side, F->fork, 0));
+    st_hot = F->side;
+    reg_counters = nullptr;
+  }
+  auto launch_hot = [&]() {
+    const int64_t gc = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_chunks * kG, kThreads), EDL_SM_COUNT * 8));
+    k_seg_chunk<kG, kC, GT, Epi><<<(unsigned)gc, kThreads, 0, st_hot>>>((const unsigned char*)grad, D4, order, seg,
+                                                                        W.counters, W.chunk_list, W.long_list, W.partial,
+                                                                        uniq, layout, epi);
+    const int64_t gf = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_long / 4 * kG, kThreads), EDL_SM_COUNT * 2));
+    k_seg_long_final<kG, kC, Epi><<<(unsigned)gf, kThreads, 0, st_hot>>>(D4, W.counters, W.long_list, W.partial, uniq,
+                                                                         layout, epi);
+  };
+  if (fork) launch_hot();
+#define EDL_DARGS (const unsigned char*)grad, D4, order, seg, seg_first, n_unique, uniq, layout, epi, reg_counters, W.long_list, W.chunk_list, long_thr
   if constexpr (kC == 1) {
     if (batch == 2)
       k_seg_direct<kG, kC, GT, Epi, 8, 1, 0, kThreads, 2><<<(unsigned)edl_cdiv(ctas, 2), kThreads, 0, st>>>(EDL_DARGS);
@@ -314,13 +390,12 @@ int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t*
     k_seg_direct<kG, kC, GT, Epi, (kC == 2 ? 4 : 2), 1><<<(unsigned)ctas, kThreads, 0, st>>>(EDL_DARGS);
   }
 #undef EDL_DARGS
-  const int64_t gc = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_chunks * kG, kThreads), EDL_SM_COUNT * 8));
-  k_seg_chunk<kG, kC, GT, Epi><<<(unsigned)gc, kThreads, 0, st>>>((const unsigned char*)grad, D4, order, seg,
-                                                                  W.counters, W.chunk_list, W.long_list, W.partial,
-                                                                  uniq, layout, epi);
-  const int64_t gf = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_long / 4 * kG, kThreads), EDL_SM_COUNT * 2));
-  k_seg_long_final<kG, kC, Epi><<<(unsigned)gf, kThreads, 0, st>>>(D4, W.counters, W.long_list, W.partial, uniq,
-                                                                 layout, epi);
+  if (fork) {
+    EDL_CUDA(cudaEventRecord(F->join, F->side));
+    EDL_CUDA(cudaStreamWaitEvent(st, F->join, 0));
+  } else {
+    launch_hot();
+  }
   EDL_LAUNCH_CHECK("k_seg_direct / k_seg_chunk");
   return EDL_OK;
 }

@@ -8,6 +8,7 @@ synchronises with the host.
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -18,7 +19,8 @@ from .parameters import ShardParameters
 
 
 class SparseStep:
-    def __init__(self, params: ShardParameters, batch_size: int, n_fields: Optional[int] = None):
+    def __init__(self, params: ShardParameters, batch_size: int, n_fields: Optional[int] = None,
+                 overlap_dedup: Optional[bool] = None):
         if params.num_shards != 1:
             raise ValueError("SparseStep is the single-shard path; use ShardedSparseStep for S > 1")
         self.params = params
@@ -41,10 +43,16 @@ class SparseStep:
         self.ws_unique = torch.empty(lib.edl_unique_workspace_bytes(N, self.key_bits, self.F, self.field_bits),
                                      dtype=torch.uint8, device=dev)
         self.ws_seg = torch.empty(lib.edl_segreduce_workspace_bytes(N, N, D), dtype=torch.uint8, device=dev)
-        # launches per step (for bench.py's gpu_launches): gather 1; unique 3/pass + 3; update 2 + memset
+        # launches per step (for bench.py's gpu_launches): gather 1; unique 3/pass + 3; update 3 (+ k_seg_classify when forked) + memset
         passes = min((self.key_bits + 7) // 8, (self.field_bits + 7) // 8)
-        self.launches_per_step = 1 + 3 * passes + 3 + 3  # + one memset node
+        fork = int(os.environ.get("EDL_SEG_FORK", "1")) != 0   # forked update adds k_seg_classify
+        self.launches_per_step = 1 + 3 * passes + 3 + 3 + int(fork)  # + one memset node
         self.last_n_unique = self.uq.n_unique
+        # The lookup does not need the dedup (it gathers by id), so the two can run side by side:
+        # the radix passes are short latency-bound kernels, the gather is one long HBM-bound one.
+        if overlap_dedup is None:
+            overlap_dedup = os.environ.get("EDL_STEP_OVERLAP", "1") == "1"
+        self.side = torch.cuda.Stream(device=dev, priority=-1) if overlap_dedup else None
 
     def lookup(self, ids: torch.Tensor) -> torch.Tensor:
         """ids int64 [B, F] on the device -> emb [B*F, dim]."""
@@ -61,8 +69,17 @@ class SparseStep:
         self.params.apply_gradients(uq, grad, self.N, self.ws_seg)
 
     def run(self, ids: torch.Tensor, grad: torch.Tensor) -> torch.Tensor:
+        if self.side is None:
+            emb = self.lookup(ids)
+            self.update(ids, grad)
+            return emb
+        cur = torch.cuda.current_stream()
+        self.side.wait_stream(cur)
+        with torch.cuda.stream(self.side):
+            uq = self.dedup(ids)
         emb = self.lookup(ids)
-        self.update(ids, grad)
+        cur.wait_stream(self.side)
+        self.update(ids, grad, uq)
         return emb
 
 

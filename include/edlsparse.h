@@ -152,7 +152,14 @@ int edl_compose_index(const int32_t* index, const int32_t* map, int64_t n, int32
  *   is stored at address base[s] + (dst - offsets[s]) rows instead of in g_out; base[s] may be another
  *   GPU's memory mapped with edl_ipc_import, so the partial sums travel over NVLink as they are made.
  * n_unique_dev: device int32 U; max_unique: host upper bound on U; n_rows: number of gradient
- * rows (= length of `order`), which bounds the scratch for hot ids. */
+ * rows (= length of `order`), which bounds the scratch for hot ids.
+ * Streams: edl_segreduce and edl_segreduce_update run the kernels for hot ids (more than 16
+ * gradient rows) on a helper stream that the library keeps per device, forked from and joined back
+ * into `stream` with events, so for the caller the call is still ordered on `stream` alone and can
+ * be captured into a CUDA graph through it.  The helper stream and its two events are created on
+ * the first call on a device, which therefore must happen outside any stream capture.  Calls from
+ * several host threads on one device are serialised over the launch sequence by a mutex.
+ * EDL_SEG_FORK=0 in the environment keeps every launch on `stream` (no helper stream is made). */
 size_t edl_segreduce_workspace_bytes(int64_t max_unique, int64_t n_rows, int dim);
 int edl_segreduce(const float* grad, int dim, const int32_t* order, const int32_t* seg_offsets,
                   const int32_t* seg_first /* nullable */, const int32_t* n_unique_dev, int64_t max_unique, int64_t n_rows,

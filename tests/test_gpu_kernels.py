@@ -357,3 +357,39 @@ def test_errors_are_reported_not_thrown(cuda):
         K.unique(torch.zeros(4, dtype=torch.int64, device=cuda), None, 0)
     with pytest.raises(_lib.EdlError, match="CUDA tensor"):
         K.unique(torch.zeros(4, dtype=torch.int64), None, 8)
+
+
+def test_update_launch_variants_agree(cuda):
+    """The update's two launch shapes (hot-id kernels on the forked helper stream, the default, and
+    all launches in a row, EDL_SEG_FORK=0) and the step with / without the dedup beside the lookup
+    give the same bits.  The switches are read once per process, so the other shapes run in a child."""
+    import subprocess, sys, os, hashlib
+    prog = r'''
+import hashlib, numpy as np, torch
+from easydl_b200.criteo import CriteoSynthetic
+from easydl_b200.optimizer import OptimizerSpec
+from easydl_b200.parameters import ShardParameters
+from easydl_b200.step import SparseStep
+dev = torch.device("cuda:0")
+rows = [50_000] * 26
+P = ShardParameters(rows, 64, OptimizerSpec.adagrad(), device=dev)
+src = CriteoSynthetic(rows, 8192, alpha=1.2)
+st = SparseStep(P, 8192)
+h = hashlib.sha256()
+for k in range(3):
+    ids = torch.from_numpy(src.ids(k)).to(dev)
+    grad = torch.from_numpy(src.grad(64, k)).to(dev)
+    emb = st.run(ids, grad)
+    torch.cuda.synchronize()
+    h.update(emb.cpu().numpy().tobytes())
+h.update(P.slab.cpu().numpy().tobytes()); h.update(P.slots[0].cpu().numpy().tobytes())
+print("DIGEST", h.hexdigest())
+'''
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    digests = []
+    for fork, overlap in (("1", "1"), ("0", "0"), ("1", "0"), ("0", "1")):
+        env = dict(os.environ, EDL_SEG_FORK=fork, EDL_STEP_OVERLAP=overlap, PYTHONPATH=root)
+        out = subprocess.run([sys.executable, "-c", prog], env=env, cwd=root, capture_output=True, text=True, timeout=600)
+        assert out.returncode == 0, out.stderr[-2000:]
+        digests.append([l for l in out.stdout.splitlines() if l.startswith("DIGEST")][0])
+    assert len(set(digests)) == 1, digests
