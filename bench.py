@@ -54,7 +54,7 @@ def parse_args():
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
     ap.add_argument("--force-sharded", action="store_true",
                     help="N=1 only: run the multi-shard code path (dedup/partition/exchange/expand) with S=1")
-    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl"],
+    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl", "slots"],
                     help="N>1: all-to-all-v by NVLink peer writes (CUDA IPC, fused with the producing "
                          "kernels) or by NCCL; auto = peer up to 4 GPUs, nccl above (measured)")
     ap.add_argument("--wire", default="f64", choices=["f64", "f32"],
@@ -228,14 +228,22 @@ def run_b200_arm(a):
         wire_dtype = torch.float64 if a.wire == "f64" else torch.float32
         if a.exchange == "auto":
             a.exchange = "peer" if world <= 4 else "nccl"
-        if world == 1:
+        slots = world > 1 and a.exchange == "slots"
+        if slots:
+            ex = None
+        elif world == 1:
             ex = SingleExchange()
         elif a.exchange == "peer":
             # receive buffers sized for 1.5x the balanced share of unique ids (hash-mod spreads evenly)
             ex = PeerExchange(dist.group.WORLD, dev, int(1.5 * N), D, wire_dtype)
         else:
             ex = TorchExchange(dist.group.WORLD, dev)
-        step = ShardedSparseStep(params, B, ex, wire_dtype=wire_dtype)
+        if slots:
+            # fixed per-pair slots, no host round trip: the step is replayed from CUDA graphs below
+            from easydl_b200.slot_step import SlotShardedStep
+            step = SlotShardedStep(params, B, group=dist.group.WORLD, wire_dtype=wire_dtype)
+        else:
+            step = ShardedSparseStep(params, B, ex, wire_dtype=wire_dtype)
 
     # distinct batches per rank: step index = batch_no * world + rank
     src = CriteoSynthetic(rows, B, a.alpha)
@@ -260,6 +268,9 @@ def run_b200_arm(a):
     if not sharded and a.optimizer == "adagrad" and not a.no_graph:
         from easydl_b200.step import GraphedStep
         graphed = [GraphedStep(step, ids_dev[i], grad_dev) for i in range(nb)]
+    elif sharded and world > 1 and a.exchange == "slots" and a.optimizer == "adagrad" and not a.no_graph:
+        from easydl_b200.slot_step import GraphedSlotStep
+        graphed = [GraphedSlotStep(step, ids_dev[i], grad_dev) for i in range(nb)]
 
     def one_step(i):
         if graphed is not None:
@@ -290,6 +301,8 @@ def run_b200_arm(a):
     if sampler:
         sampler.active = False
     ms = t_begin.elapsed_time(t_end)
+    if hasattr(step, "check"):
+        step.check()            # slot exchange: raises if a slot overflowed or a fence timed out
     t_ms = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)

@@ -68,6 +68,11 @@ PROTOTYPES = {
     "edl_ipc_close": (_int, [_p]),
     "edl_peer_copy": (_int, [_p, _p, _sz, _p]),
     "edl_peer_signal_wait": (_int, [_p, _p, _int, _int, _i64, _p]),
+    "edl_peer_signal_wait_counter": (_int, [_p, _p, _int, _int, _p, _p]),
+    "edl_slot_send": (_int, [_p, _int, _p, _int, _p, _i64, _p, _p, _i64, _p]),
+    "edl_slot_positions": (_int, [_p, _i64, _p, _p, _int, _i64, _p, _p]),
+    "edl_slot_compact": (_int, [_p, _p, _int, _i64, _i64, _p, _p, _p, _p]),
+    "edl_remap_index": (_int, [_p, _p, _i64, _p, _p, _p]),
 }
 
 _lib = None

@@ -193,6 +193,60 @@ def compose_index(index: torch.Tensor, mapping: torch.Tensor):
     return out
 
 
+# ------------------------------------------------------------------------------- A7 (slot rounds)
+def slot_send(rows: torch.Tensor, offsets: torch.Tensor, dst_bases: torch.Tensor, slot_limit: int,
+              count_ptrs: Optional[torch.Tensor], err: torch.Tensor, n_max: int):
+    """rows (partition order, any dtype with 8-byte-multiple rows) -> this rank's slot at every peer."""
+    lib = _lib.load()
+    _need(offsets, torch.int32, "offsets")
+    _need(dst_bases, torch.int64, "dst_bases")
+    _need(err, torch.int32, "err")
+    if not rows.is_contiguous():
+        raise ValueError("rows must be contiguous")
+    row_bytes = rows.element_size() * (rows.numel() // max(rows.shape[0], 1)) if rows.dim() > 1 else rows.element_size()
+    check(lib.edl_slot_send(_ptr(rows), row_bytes, _ptr(offsets), offsets.numel() - 1, _ptr(dst_bases),
+                            slot_limit, _ptr(count_ptrs), _ptr(err), n_max, _stream()), "edl_slot_send")
+
+
+def slot_positions(pos: torch.Tensor, n_dev: Optional[torch.Tensor], offsets: torch.Tensor, slot_stride: int,
+                   out: Optional[torch.Tensor] = None):
+    lib = _lib.load()
+    _need(pos, torch.int32, "pos")
+    _need(offsets, torch.int32, "offsets")
+    if out is None:
+        out = torch.empty_like(pos)
+    check(lib.edl_slot_positions(_ptr(pos), pos.numel(), _ptr(n_dev), _ptr(offsets), offsets.numel() - 1,
+                                 slot_stride, _ptr(out), _stream()), "edl_slot_positions")
+    return out
+
+
+def slot_compact(keys_slots: torch.Tensor, counts: torch.Tensor, slot_stride: int, slot_limit: int,
+                 keys_out: torch.Tensor, map_out: torch.Tensor, n_out: torch.Tensor):
+    lib = _lib.load()
+    _need(keys_slots, torch.int64, "keys_slots")
+    _need(counts, torch.int32, "counts")
+    _need(keys_out, torch.int64, "keys_out")
+    _need(map_out, torch.int32, "map_out")
+    _need(n_out, torch.int32, "n_out")
+    S = counts.numel()
+    if keys_out.numel() < S * slot_limit or map_out.numel() < S * slot_limit:
+        raise ValueError("slot_compact: outputs smaller than num_slots * slot_limit")
+    check(lib.edl_slot_compact(_ptr(keys_slots), _ptr(counts), S, slot_stride, slot_limit, _ptr(keys_out),
+                               _ptr(map_out), _ptr(n_out), _stream()), "edl_slot_compact")
+
+
+def remap_index(index: torch.Tensor, mapping: torch.Tensor, n_dev: Optional[torch.Tensor],
+                out: Optional[torch.Tensor] = None):
+    lib = _lib.load()
+    _need(index, torch.int32, "index")
+    _need(mapping, torch.int32, "mapping")
+    if out is None:
+        out = torch.empty_like(index)
+    check(lib.edl_remap_index(_ptr(index), _ptr(mapping), index.numel(), _ptr(n_dev), _ptr(out), _stream()),
+          "edl_remap_index")
+    return out
+
+
 def scatter_rows(rows: torch.Tensor, pos: torch.Tensor, out: torch.Tensor, *,
                  n_dev: Optional[torch.Tensor] = None):
     lib = _lib.load()
@@ -239,8 +293,9 @@ def segreduce_update(slab: torch.Tensor, slot0: torch.Tensor, slot1: Optional[to
                      layout: Optional[torch.Tensor], opt: OptParams,
                      touched: Optional[torch.Tensor] = None,
                      workspace: Optional[torch.Tensor] = None,
-                     seg_first: Optional[torch.Tensor] = None):
-    """grad rows may be float32 (a worker's raw gradient) or float64 (exchanged partial sums)."""
+                     seg_first: Optional[torch.Tensor] = None, n_rows: Optional[int] = None):
+    """grad rows may be float32 (a worker's raw gradient) or float64 (exchanged partial sums).
+    n_rows: bound on the number of gradient rows referenced (default: all rows of `grad`)."""
     lib = _lib.load()
     _need(slab, torch.float32, "slab")
     _need(slot0, torch.float32, "slot0")
@@ -251,7 +306,7 @@ def segreduce_update(slab: torch.Tensor, slot0: torch.Tensor, slot1: Optional[to
     dim = slab.shape[1]
     if grad.shape[1] != dim:
         raise ValueError("grad and slab dims differ")
-    n_rows = grad.shape[0]
+    n_rows = grad.shape[0] if n_rows is None else int(n_rows)
     need = lib.edl_segreduce_workspace_bytes(max_unique, n_rows, dim)
     if workspace is None or workspace.numel() < need:
         workspace = _ws(need, slab.device)

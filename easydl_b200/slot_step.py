@@ -1,0 +1,325 @@
+"""The sharded sparse step without a host round trip.
+
+ShardedSparseStep needs the count matrix of every all-to-all-v on the host, so the GPU drains once
+per step and the host issues ~45 launches behind it.  Here each receive buffer is cut into one
+fixed slot per sending rank (csrc/slots.cu): senders need only their own partition offsets, which
+stay on the device, and row counts travel with the data.  The step is then a fixed launch sequence
+
+    A  dedup(local ids) -> partition by owner -> keys into my slot at every owner        | fence
+    B  owner: gather the rows of every requester's slot straight into that requester     | fence
+    C  expand my rows to emb;  reduce grad per unique id straight into the owners' slots | fence
+    D  owner: compact the key slots (peer-rank order) -> dedup -> reduce -> optimizer
+
+with no size known to the host: it is issued without synchronising and can be replayed from a CUDA
+graph (GraphedSlotStep).  Same arithmetic and the same merge order as ShardedSparseStep.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib
+from . import kernels as K
+from .exchange import _RawDeviceMemory
+from .parameters import ShardParameters
+
+
+def _align(n: int, a: int = 256) -> int:
+    return (n + a - 1) // a * a
+
+
+class SlotBuffers:
+    """One rank's receive buffers: per generation (two, alternated step by step) a keys, a rows
+    and a grads region of `world` slots x `stride` rows each plus `world` int32 row counts; then
+    the fence flags, the fence round counter and the overflow flag.  Allocated with edl_peer_alloc
+    (zeroed) so that other ranks can map it with CUDA IPC."""
+
+    REGIONS = ("keys", "rows", "grads", "counts")
+
+    def __init__(self, world: int, rank: int, device, stride: int, dim: int, wire_dtype=torch.float64):
+        self.lib = _lib.load()
+        self.world, self.rank, self.device = int(world), int(rank), torch.device(device)
+        self.stride, self.dim, self.wire_dtype = int(stride), int(dim), wire_dtype
+        wire_b = 8 if wire_dtype == torch.float64 else 4
+        self.row_bytes = {"keys": 8, "rows": dim * 4, "grads": dim * wire_b, "counts": 4}
+        self.off, off = {}, 0
+        for gen in (0, 1):
+            for r in self.REGIONS:
+                self.off[(gen, r)] = off
+                rows = self.world * self.stride if r != "counts" else self.world
+                off += _align(rows * self.row_bytes[r])
+        self.flags_off = off                  # [world + 1] int64 arrival values, [world + 1] = timeout mark
+        self.counter_off = off + 8 * (self.world + 1)
+        self.err_off = self.counter_off + 8
+        off += _align(8 * (self.world + 1) + 16, 1024)
+        self.nbytes = off
+        ptr = C.c_void_p()
+        _lib.check(self.lib.edl_peer_alloc(C.byref(ptr), self.nbytes), "edl_peer_alloc")
+        self.own_ptr = ptr.value
+        self.own = torch.as_tensor(_RawDeviceMemory(self.own_ptr, self.nbytes), device=self.device)
+        self.base: List[int] = []
+        self._imported = []
+
+    # ---- wiring
+    def connect_ipc(self, group):
+        import torch.distributed as dist
+        handle = C.create_string_buffer(64)
+        _lib.check(self.lib.edl_ipc_export(self.own_ptr, handle), "edl_ipc_export")
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle.raw), group=group)
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                self.base.append(self.own_ptr)
+            else:
+                p = C.c_void_p()
+                _lib.check(self.lib.edl_ipc_import(h, C.byref(p)), "edl_ipc_import")
+                self.base.append(p.value)
+                self._imported.append(p.value)
+        self._tables()
+        dist.barrier(group=group)
+
+    def connect_local(self, all_buffers: Sequence["SlotBuffers"]):
+        """Virtual ranks of one process on one GPU (tests): the peers' buffers are plain pointers."""
+        self.base = [b.own_ptr for b in all_buffers]
+        self._tables()
+
+    def close(self):
+        for p in self._imported:
+            self.lib.edl_ipc_close(p)
+        self._imported = []
+        if self.own_ptr:
+            self.lib.edl_peer_free(self.own_ptr)
+        self.own_ptr = None
+
+    # ---- views and address tables
+    def _slot_addr(self, peer: int, gen: int, region: str, slot: int) -> int:
+        rb = self.row_bytes[region]
+        rows = self.stride if region != "counts" else 1
+        return self.base[peer] + self.off[(gen, region)] + slot * rows * rb
+
+    def _tables(self):
+        me, W, dev = self.rank, self.world, self.device
+        def table(fn):
+            return torch.tensor([fn(d) for d in range(W)], dtype=torch.int64, device=dev)
+        self.keys_dst = [table(lambda d: self._slot_addr(d, g, "keys", me)) for g in (0, 1)]
+        self.count_dst = [table(lambda d: self._slot_addr(d, g, "counts", me)) for g in (0, 1)]
+        self.grads_dst = [table(lambda d: self._slot_addr(d, g, "grads", me)) for g in (0, 1)]
+        self.flag_ptrs = torch.tensor([b + self.flags_off for b in self.base], dtype=torch.int64, device=dev)
+        self.own_flags = self.own[self.flags_off:self.flags_off + 8 * (W + 1)].view(torch.int64)
+        self.counter = self.own[self.counter_off:self.counter_off + 8].view(torch.int64)
+        self.err = self.own[self.err_off:self.err_off + 4].view(torch.int32)
+
+    def own_region(self, gen: int, region: str) -> torch.Tensor:
+        """My receive region as [world * stride, ...] (slot-space rows)."""
+        rb = self.row_bytes[region]
+        rows = self.world * self.stride if region != "counts" else self.world
+        o = self.off[(gen, region)]
+        raw = self.own[o:o + rows * rb]
+        if region == "keys":
+            return raw.view(torch.int64)
+        if region == "counts":
+            return raw.view(torch.int32)
+        return raw.view(torch.float32 if region == "rows" else self.wire_dtype).view(rows, self.dim)
+
+    def remote_rows_slot(self, peer: int, gen: int, n_rows: int) -> torch.Tensor:
+        """My slot of the rows region of `peer` (peer-mapped memory), as [n_rows, dim] fp32."""
+        ptr = self._slot_addr(peer, gen, "rows", self.rank)
+        nb = n_rows * self.row_bytes["rows"]
+        t = torch.as_tensor(_RawDeviceMemory(ptr, nb), device=self.device)
+        return t.view(torch.float32).view(n_rows, self.dim)
+
+    def fence(self):
+        rc = self.lib.edl_peer_signal_wait_counter(self.flag_ptrs.data_ptr(), self.own_flags.data_ptr(), self.rank,
+                                                   self.world, self.counter.data_ptr(),
+                                                   torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "edl_peer_signal_wait_counter")
+
+
+class SlotShardedStep:
+    """One rank of the host-sync-free sharded step.  `slot_limit` bounds the rows one rank may send
+    to one owner in a step (it sizes the owner-side launches); memory is reserved for the worst case
+    (`stride` = batch ids), so a longer group is cut, flagged, and reported by check()."""
+
+    def __init__(self, params: ShardParameters, batch_size: int, buffers: Optional[SlotBuffers] = None, *,
+                 group=None, n_fields: Optional[int] = None, wire_dtype=torch.float64,
+                 slot_slack: float = 1.5):
+        self.params = params
+        self.S, self.rank = params.num_shards, params.shard
+        self.F = params.layout.n_tables if n_fields is None else n_fields
+        self.B = int(batch_size)
+        self.N = self.B * self.F
+        self.dim, self.wire_dtype = params.dim, wire_dtype
+        dev = params.device
+        self.device = dev
+        self.limit = min(self.N, int(slot_slack * self.N / self.S) + 1024)
+        if buffers is None:
+            buffers = SlotBuffers(self.S, self.rank, dev, self.N, self.dim, wire_dtype)
+            if group is not None:
+                buffers.connect_ipc(group)
+        self.buf = buffers
+        self.gen = 0
+        self.field_base = torch.from_numpy(params.layout.key_base[:self.F].copy()).to(dev)
+        self.key_bits, self.field_bits = params.layout.key_bits, params.layout.field_bits
+        lib = _lib.load()
+        N, R = self.N, self.S * self.limit
+        i32 = dict(dtype=torch.int32, device=dev)
+        self.uq = K.UniqueResult(
+            uniq=torch.empty(N, dtype=torch.int64, device=dev), inverse=torch.empty(N, **i32), counts=None,
+            order=torch.empty(N, **i32), seg_offsets=torch.empty(N + 1, **i32),
+            n_unique=torch.zeros(1, **i32), n=N, seg_first=torch.empty(N, **i32))
+        self.uq2 = K.UniqueResult(
+            uniq=torch.empty(R, dtype=torch.int64, device=dev), inverse=None, counts=None,
+            order=torch.empty(R, **i32), seg_offsets=torch.empty(R + 1, **i32),
+            n_unique=torch.zeros(1, **i32), n=R, seg_first=torch.empty(R, **i32))
+        self.keys_c = torch.empty(R, dtype=torch.int64, device=dev)
+        self.map_c = torch.empty(R, **i32)
+        self.n_recv = torch.zeros(1, **i32)
+        self.order2 = torch.empty(R, **i32)
+        self.first2 = torch.empty(R, **i32)
+        self.slotpos = torch.empty(N, **i32)
+        self.emb = torch.empty((N, self.dim), dtype=torch.float32, device=dev)
+        self.ws_u1 = torch.empty(lib.edl_unique_workspace_bytes(N, self.key_bits, self.F, self.field_bits),
+                                 dtype=torch.uint8, device=dev)
+        self.ws_u2 = torch.empty(lib.edl_unique_workspace_bytes(R, self.key_bits, 0, 0), dtype=torch.uint8, device=dev)
+        self.ws_part = torch.empty(lib.edl_partition_mod_workspace_bytes(N, self.S), dtype=torch.uint8, device=dev)
+        self.ws_seg = torch.empty(max(lib.edl_segreduce_workspace_bytes(N, N, self.dim),
+                                      lib.edl_segreduce_workspace_bytes(R, R, self.dim)), dtype=torch.uint8, device=dev)
+        self.S_const = torch.tensor([self.S], dtype=torch.int64, device=dev)
+        self.part = None
+        self.last_n_unique = self.uq.n_unique
+        passes1 = min((self.key_bits + 7) // 8, (self.field_bits + 7) // 8) if self.field_bits else (self.key_bits + 7) // 8
+        passes2 = (self.key_bits + 7) // 8
+        # A: unique, partition 4, send 1; B: S gathers; C: positions, compose, expand, 2 torch ops, reduce 4;
+        # D: compact, unique, 2 remaps, update 4; 3 fences
+        self.launches_per_step = (3 * passes1 + 3) + 4 + 1 + self.S + 3 + 2 + 4 + 1 + (3 * passes2 + 3) + 2 + 4 + 3
+
+    # ------------------------------------------------------------------ phases
+    def phase_a(self, ids: torch.Tensor):
+        b, g = self.buf, self.gen
+        K.unique(ids.reshape(-1), self.field_base, self.key_bits, field_bits=self.field_bits, want_inverse=True,
+                 want_counts=False, out=self.uq, workspace=self.ws_u1)
+        self.part = K.partition_mod(self.uq.uniq, self.params.layout_dev, self.S, n_dev=self.uq.n_unique,
+                                    workspace=self.ws_part)
+        K.slot_send(self.part.keys, self.part.offsets, b.keys_dst[g], self.limit, b.count_dst[g], b.err, self.N)
+
+    def phase_b(self):
+        b, g = self.buf, self.gen
+        keys = b.own_region(g, "keys")
+        counts = b.own_region(g, "counts")
+        for s in range(self.S):
+            k = keys[s * b.stride:s * b.stride + self.limit]
+            K.gather_keys(self.params.slab, k, self.params._layout_arg, n_dev=counts[s:s + 1],
+                          out=b.remote_rows_slot(s, g, self.limit))
+
+    def phase_c_expand(self) -> torch.Tensor:
+        b, g, uq, part = self.buf, self.gen, self.uq, self.part
+        K.slot_positions(part.pos, uq.n_unique, part.offsets, b.stride, out=self.slotpos)
+        idx = K.compose_index(uq.inverse, self.slotpos)
+        K.expand(b.own_region(g, "rows"), idx, out=self.emb)
+        return self.emb
+
+    def phase_c_reduce(self, grad: torch.Tensor):
+        b, g, uq, part = self.buf, self.gen, self.uq, self.part
+        table = torch.cat([self.S_const, part.offsets.to(torch.int64), b.grads_dst[g]])
+        K.segreduce(grad, uq.order, uq.seg_offsets, uq.n_unique, self.N, seg_first=uq.seg_first, out_pos=part.pos,
+                    out=None, out_dtype=self.wire_dtype, dst_table=table, workspace=self.ws_seg)
+
+    def phase_c(self, grad: torch.Tensor) -> torch.Tensor:
+        emb = self.phase_c_expand()
+        self.phase_c_reduce(grad)
+        return emb
+
+    def phase_d(self):
+        b, g, uq2 = self.buf, self.gen, self.uq2
+        K.slot_compact(b.own_region(g, "keys"), b.own_region(g, "counts"), b.stride, self.limit, self.keys_c,
+                       self.map_c, self.n_recv)
+        K.unique(self.keys_c, None, self.key_bits, want_inverse=False, want_counts=False, n_dev=self.n_recv,
+                 out=uq2, workspace=self.ws_u2)
+        K.remap_index(uq2.order, self.map_c, self.n_recv, out=self.order2)
+        K.remap_index(uq2.seg_first, self.map_c, uq2.n_unique, out=self.first2)
+        slotted = K.UniqueResult(uniq=uq2.uniq, inverse=None, counts=None, order=self.order2,
+                                 seg_offsets=uq2.seg_offsets, n_unique=uq2.n_unique, n=uq2.n, seg_first=self.first2)
+        self.params.apply_gradients(slotted, b.own_region(g, "grads"), uq2.n, self.ws_seg, n_rows=uq2.n)
+        self.gen ^= 1
+
+    # ------------------------------------------------------------------ drivers
+    def lookup(self, ids: torch.Tensor) -> torch.Tensor:
+        """Forward half on a real rank (one process per GPU): emb [B*F, dim].  No host synchronisation."""
+        self.phase_a(ids)
+        self.buf.fence()
+        self.phase_b()
+        self.buf.fence()
+        return self.phase_c_expand()
+
+    def update(self, ids: Optional[torch.Tensor], grad: torch.Tensor, uq=None):
+        """Backward half for the ids of the preceding lookup()."""
+        self.phase_c_reduce(grad)
+        self.buf.fence()
+        self.phase_d()
+
+    def run(self, ids: torch.Tensor, grad: torch.Tensor) -> torch.Tensor:
+        emb = self.lookup(ids)
+        self.update(ids, grad)
+        return emb
+
+    def check(self):
+        """Synchronise and raise if a slot overflowed or a fence timed out since the last check."""
+        torch.cuda.synchronize(self.device)
+        err = int(self.buf.err.item())
+        late = int(self.buf.own_flags[self.S].item())
+        if err:
+            raise RuntimeError(f"SlotShardedStep: more than slot_limit={self.limit} ids for one owner in a step; "
+                               "raise slot_slack")
+        if late:
+            raise RuntimeError("SlotShardedStep: a peer did not reach the exchange fence (timeout)")
+
+
+def run_virtual(steps: Sequence[SlotShardedStep], ids: Sequence[torch.Tensor], grads: Sequence[torch.Tensor]):
+    """All ranks of a step as virtual ranks on one GPU and one stream (tests): phase by phase over
+    the ranks, which orders the rounds the way the fences do between real GPUs."""
+    for st, i in zip(steps, ids):
+        st.phase_a(i)
+    for st in steps:
+        st.phase_b()
+    embs = [st.phase_c(g) for st, g in zip(steps, grads)]
+    for st in steps:
+        st.phase_d()
+    return embs
+
+
+class GraphedSlotStep:
+    """SlotShardedStep replayed from CUDA graphs for one fixed (ids, grad) buffer pair: one graph per
+    buffer generation, replayed alternately.  Adagrad only (Adam's rate is a by-value argument that
+    changes every step).  Every rank must construct and replay in lock step."""
+
+    def __init__(self, step: SlotShardedStep, ids: torch.Tensor, grad: torch.Tensor):
+        from ._lib import EDL_OPT_ADAGRAD
+        if step.params.opt.kind != EDL_OPT_ADAGRAD:
+            raise ValueError("GraphedSlotStep supports Adagrad only")
+        self.step, self.ids, self.grad = step, ids, grad
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):        # both generations once, outside capture
+            step.run(ids, grad)
+            step.run(ids, grad)
+        cur.wait_stream(side)
+        torch.cuda.synchronize()
+        host_step = step.params.step
+        self.graphs = [None, None]
+        for _ in (0, 1):                     # in the order the generations come up next
+            gen = step.gen
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                step.run(ids, grad)
+            self.graphs[gen] = g
+        step.params.step = host_step
+
+    def run(self) -> torch.Tensor:
+        st = self.step                        # the generation lives on the step: several graphed
+        self.graphs[st.gen].replay()          # (ids, grad) pairs may share one step
+        st.gen ^= 1
+        st.params.step += 1
+        return st.emb

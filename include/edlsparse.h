@@ -263,6 +263,40 @@ int edl_peer_copy(void* dst, const void* src, size_t bytes, edl_stream_t stream)
  * [world] is set to -1 if the wait timed out.  One rank per GPU. */
 int edl_peer_signal_wait(const int64_t* peer_flag_ptrs_dev, int64_t* own_flags, int me, int world,
                          int64_t value, edl_stream_t stream);
+/* The same with the round number kept on the device: the kernel increments *counter_dev and
+ * publishes the new value, so a CUDA graph that contains it signals a fresh round on every replay. */
+int edl_peer_signal_wait_counter(const int64_t* peer_flag_ptrs_dev, int64_t* own_flags, int me, int world,
+                                 int64_t* counter_dev, edl_stream_t stream);
+
+/* ---- A7 rounds over fixed per-pair slots: no size ever reaches the host -------------------
+ * (replaces the worker <-> PS RPC of the lineage, like the section above; no reference file.)
+ * A receive buffer is `num_slots` (= world size) slots of `slot_stride` rows; slot s is written only
+ * by rank s, so a sender needs only its own partition offsets, which edl_partition_mod leaves on
+ * the device.  Row counts travel with the data.  Every launch below has a fixed grid, so the whole
+ * sharded step can be captured into a CUDA graph.
+ *
+ * edl_slot_send    : rows[p] for p in [offsets[d], offsets[d+1]) -> dst_bases[d] + (p - offsets[d]) rows
+ *                    (dst_bases_dev: device array of num_slots addresses, usually this rank's slot in
+ *                    every peer's buffer); count_ptrs_dev (nullable): device array of num_slots
+ *                    addresses of int32 cells that receive the group sizes.  Groups longer than
+ *                    slot_limit are cut there and *err_dev |= 1 (check it after the step).
+ *                    n_max: host bound on offsets[num_slots] (sizes the grid only).
+ * edl_slot_positions: out[u] = d * slot_stride + (pos[u] - offsets[d]), the slot-space row of
+ *                    partition position pos[u] (receiver side of the rows round).
+ * edl_slot_compact : owner side: slots of keys with counts[s] valid rows -> contiguous keys_out in
+ *                    slot (= peer rank) order, map_out[i] = slot-space row of keys_out[i], *n_out.
+ * edl_remap_index  : out[i] = map[index[i]] for i < *n_dev (edl_compose_index with a device count):
+ *                    turns the `order` / `seg_first` of edl_unique(keys_out) into slot-space rows. */
+int edl_slot_send(const void* rows, int row_bytes, const int32_t* offsets_dev, int num_slots,
+                  const int64_t* dst_bases_dev, int64_t slot_limit, const int64_t* count_ptrs_dev,
+                  int32_t* err_dev, int64_t n_max, edl_stream_t stream);
+int edl_slot_positions(const int32_t* pos, int64_t n_max, const int32_t* n_dev, const int32_t* offsets_dev,
+                       int num_slots, int64_t slot_stride, int32_t* out, edl_stream_t stream);
+int edl_slot_compact(const int64_t* keys_slots, const int32_t* counts_dev, int num_slots, int64_t slot_stride,
+                     int64_t slot_limit, int64_t* keys_out, int32_t* map_out, int32_t* n_out_dev,
+                     edl_stream_t stream);
+int edl_remap_index(const int32_t* index, const int32_t* map, int64_t n_max, const int32_t* n_dev,
+                    int32_t* out, edl_stream_t stream);
 
 #ifdef __cplusplus
 }

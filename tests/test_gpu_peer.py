@@ -75,7 +75,8 @@ def test_peer_alloc_copy_and_fence_world_of_one(cuda):
     assert lib.edl_peer_free(p.value) == 0
 
 
-@pytest.mark.parametrize("mode,opt", [("peer", "adam"), ("nccl", "adagrad")])
+@pytest.mark.parametrize("mode,opt", [("peer", "adam"), ("nccl", "adagrad"), ("slots", "adam"),
+                                      ("slots-graph", "adagrad")])
 def test_real_ranks_match_oracle(cuda, mode, opt):
     n = torch.cuda.device_count()
     if n < 2:

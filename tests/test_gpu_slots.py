@@ -1,0 +1,163 @@
+"""The host-sync-free sharded step (easydl_b200/slot_step.py, csrc/slots.cu) on ONE GPU: the slot
+kernels one by one, then S virtual ranks phase by phase against the oracle's global float64 pass
+and against ShardedSparseStep (same arithmetic, same merge order -> same bits)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import edl_oracle as O
+
+pytestmark = pytest.mark.gpu
+RTOL, ATOL = 1e-6, 1e-9
+
+
+def dev(a, cuda):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(cuda)
+
+
+def test_slot_send_positions_compact_remap(cuda):
+    from easydl_b200 import kernels as K
+    rng = np.random.default_rng(11)
+    S, stride, limit, dim = 3, 64, 40, 4
+    offs = np.array([0, 17, 17, 50], dtype=np.int32)            # middle group empty
+    rows = rng.standard_normal((50, dim)).astype(np.float64)
+    keys = rng.integers(0, 1 << 40, size=50, dtype=np.int64)
+    bufs_r = [torch.zeros((stride, dim), dtype=torch.float64, device=cuda) for _ in range(S)]
+    keyslots = torch.full((S * stride,), -1, dtype=torch.int64, device=cuda)
+    counts = torch.full((S,), -7, dtype=torch.int32, device=cuda)
+    err = torch.zeros(1, dtype=torch.int32, device=cuda)
+    d_offs = dev(offs, cuda)
+    K.slot_send(dev(rows, cuda), d_offs, torch.tensor([b.data_ptr() for b in bufs_r], dtype=torch.int64, device=cuda),
+                limit, None, err, 64)
+    kb = torch.tensor([keyslots.data_ptr() + s * stride * 8 for s in range(S)], dtype=torch.int64, device=cuda)
+    cp = torch.tensor([counts.data_ptr() + 4 * s for s in range(S)], dtype=torch.int64, device=cuda)
+    K.slot_send(dev(keys, cuda), d_offs, kb, limit, cp, err, 64)
+    assert int(err.item()) == 0
+    for s in range(S):
+        c = offs[s + 1] - offs[s]
+        assert np.array_equal(bufs_r[s][:c].cpu().numpy(), rows[offs[s]:offs[s + 1]])
+        assert float(bufs_r[s][c:].abs().sum()) == 0.0
+        assert np.array_equal(keyslots[s * stride:s * stride + c].cpu().numpy(), keys[offs[s]:offs[s + 1]])
+    assert counts.cpu().tolist() == [17, 0, 33]
+    # positions: partition position -> slot-space row
+    pos = dev(rng.permutation(50).astype(np.int32), cuda)
+    n_dev = torch.tensor([45], dtype=torch.int32, device=cuda)
+    sp = K.slot_positions(pos, n_dev, d_offs, stride, out=torch.full((50,), -1, dtype=torch.int32, device=cuda))
+    p = pos.cpu().numpy()
+    d = np.searchsorted(offs[1:], p, side="right")
+    want = d * stride + (p - offs[d])
+    assert np.array_equal(sp.cpu().numpy()[:45], want[:45]) and np.all(sp.cpu().numpy()[45:] == -1)
+    # compact: slot order, counts clipped at the limit
+    keys_c = torch.empty(S * limit, dtype=torch.int64, device=cuda)
+    map_c = torch.empty(S * limit, dtype=torch.int32, device=cuda)
+    n_out = torch.zeros(1, dtype=torch.int32, device=cuda)
+    K.slot_compact(keyslots, counts, stride, limit, keys_c, map_c, n_out)
+    assert int(n_out.item()) == 50
+    assert np.array_equal(keys_c[:50].cpu().numpy(), keys)
+    assert np.array_equal(map_c[:50].cpu().numpy(), np.concatenate([np.arange(17), 2 * stride + np.arange(33)]))
+    # remap with a device count
+    idx = dev(rng.integers(0, 50, size=80).astype(np.int32), cuda)
+    out = K.remap_index(idx, map_c, torch.tensor([60], dtype=torch.int32, device=cuda),
+                        out=torch.full((80,), -5, dtype=torch.int32, device=cuda))
+    assert np.array_equal(out[:60].cpu().numpy(), map_c.cpu().numpy()[idx.cpu().numpy()[:60]])
+    assert np.all(out[60:].cpu().numpy() == -5)
+    # overflow: a group longer than the limit is cut and flagged
+    K.slot_send(dev(keys, cuda), d_offs, kb, 20, cp, err, 64)
+    assert int(err.item()) == 1 and counts.cpu().tolist() == [17, 0, 20]
+
+
+def test_fence_with_device_counter_world_of_one(cuda):
+    import ctypes as C
+    from easydl_b200 import _lib
+    lib = _lib.load()
+    flags = torch.zeros(2, dtype=torch.int64, device=cuda)
+    counter = torch.zeros(1, dtype=torch.int64, device=cuda)
+    ptrs = torch.tensor([flags.data_ptr()], dtype=torch.int64, device=cuda)
+    st = torch.cuda.current_stream().cuda_stream
+    for _ in range(3):
+        assert lib.edl_peer_signal_wait_counter(ptrs.data_ptr(), flags.data_ptr(), 0, 1, counter.data_ptr(), st) == 0
+    torch.cuda.synchronize()
+    assert flags.cpu().tolist() == [3, 0] and int(counter.item()) == 3
+
+
+def _virtual(cuda, rows, dim, S, opt_name, batch, wire=torch.float64, slack=1.5):
+    from easydl_b200.optimizer import OptimizerSpec
+    from easydl_b200.parameters import ShardParameters
+    from easydl_b200.slot_step import SlotBuffers, SlotShardedStep
+    po = OptimizerSpec.adagrad() if opt_name == "adagrad" else OptimizerSpec.adam()
+    params = [ShardParameters(rows, dim, po, S, s, device=cuda) for s in range(S)]
+    bufs = [SlotBuffers(S, s, cuda, batch * len(rows), dim, wire) for s in range(S)]
+    for b in bufs:
+        b.connect_local(bufs)
+    steps = [SlotShardedStep(p, batch, b, wire_dtype=wire, slot_slack=slack) for p, b in zip(params, bufs)]
+    return params, bufs, steps
+
+
+@pytest.mark.parametrize("S,opt", [(1, "adagrad"), (2, "adagrad"), (4, "adam"), (6, "adagrad"), (8, "adam")])
+def test_slot_step_matches_global_oracle(cuda, S, opt):
+    from easydl_b200.slot_step import run_virtual
+    from test_gpu_sharded import _compare_state, bits
+    rows, dim, batch, steps = [5000, 301, 70001, 11, 6], 32, 512, 3
+    params, bufs, st = _virtual(cuda, rows, dim, S, opt, batch)
+    oo = O.OptimizerSpec.adagrad() if opt == "adagrad" else O.OptimizerSpec.adam()
+    osh = [O.OracleShard(rows, dim, oo, S, s) for s in range(S)]
+    bases = O.key_bases(rows)
+    for k in range(steps):
+        kw, gw, di, dg = [], [], [], []
+        for r in range(S):
+            _, ids, _ = O.criteo_batch(rows, batch, 1.05, step=k * 8 + r)
+            g = O.synthetic_grad(ids.size, dim, step=k * 8 + r)
+            kw.append(O.fuse_keys(ids, bases)); gw.append(g)
+            di.append(dev(ids, cuda)); dg.append(dev(g, cuda))
+        embs = run_virtual(st, di, dg)
+        want = O.sharded_step(osh, kw, gw)
+        for r in range(S):
+            got = embs[r].cpu().numpy()
+            if k == 0:
+                assert np.array_equal(bits(got), bits(want[r])), f"emb step {k} rank {r}"
+            err = np.abs(got.astype(np.float64) - want[r])
+            assert np.all(err <= ATOL + RTOL * np.abs(want[r])), f"emb step {k} rank {r}: {err.max():.3e}"
+    for s in st:
+        s.check()
+    _compare_state(cuda, params, osh, oo.n_slots)
+    for b in bufs:
+        b.close()
+
+
+def test_slot_step_same_bits_as_packed_exchange(cuda):
+    """Same kernels, same merge order: identical shard state to ShardedSparseStep (lock-step ranks)."""
+    from easydl_b200.exchange import run_lockstep
+    from easydl_b200.optimizer import OptimizerSpec
+    from easydl_b200.parameters import ShardParameters
+    from easydl_b200.sharded_step import ShardedSparseStep
+    from easydl_b200.slot_step import run_virtual
+    rows, dim, batch, S = [20000, 3000, 17], 64, 2048, 4
+    params, bufs, st = _virtual(cuda, rows, dim, S, "adagrad", batch)
+    ref_p = [ShardParameters(rows, dim, OptimizerSpec.adagrad(), S, s, device=cuda) for s in range(S)]
+    ref_st = [ShardedSparseStep(p, batch) for p in ref_p]
+    for k in range(3):
+        di, dg = [], []
+        for r in range(S):
+            _, ids, _ = O.criteo_batch(rows, batch, 1.2, step=k * 8 + r)
+            di.append(dev(ids, cuda)); dg.append(dev(O.synthetic_grad(ids.size, dim, step=k * 8 + r), cuda))
+        embs = run_virtual(st, di, dg)
+        ref = run_lockstep([s.gen_step(i, g) for s, i, g in zip(ref_st, di, dg)])
+        for a, b in zip(embs, ref):
+            assert torch.equal(a, b)
+    for p, q in zip(params, ref_p):
+        assert torch.equal(p.slab, q.slab) and torch.equal(p.slots[0], q.slots[0]) and p.step == q.step
+    for b in bufs:
+        b.close()
+
+
+def test_slot_overflow_is_reported(cuda):
+    from easydl_b200.slot_step import run_virtual
+    rows, dim, batch, S = [100000], 16, 4096, 2
+    params, bufs, st = _virtual(cuda, rows, dim, S, "adagrad", batch, slack=0.0)   # limit = 1024 rows per pair
+    _, ids, _ = O.criteo_batch(rows, batch, 0.5, step=0)
+    g = O.synthetic_grad(ids.size, dim, step=0)
+    run_virtual(st, [dev(ids, cuda)] * S, [dev(g, cuda)] * S)
+    with pytest.raises(RuntimeError, match="slot_limit"):
+        st[0].check()
+    for b in bufs:
+        b.close()
