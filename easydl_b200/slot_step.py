@@ -16,6 +16,7 @@ graph (GraphedSlotStep).  Same arithmetic and the same merge order as ShardedSpa
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional, Sequence
 
 import torch
@@ -187,6 +188,12 @@ class SlotShardedStep:
         self.ws_seg = torch.empty(max(lib.edl_segreduce_workspace_bytes(N, N, self.dim),
                                       lib.edl_segreduce_workspace_bytes(R, R, self.dim)), dtype=torch.uint8, device=dev)
         self.S_const = torch.tensor([self.S], dtype=torch.int64, device=dev)
+        # helper streams (real ranks): the owner-side dedup of the received keys runs beside the rest
+        # of the forward half, the NVLink-bound gathers into the peers beside the local HBM-bound one
+        self.overlap = os.environ.get("EDL_SLOT_OVERLAP", "1") == "1"
+        self.side = torch.cuda.Stream(device=dev, priority=-1) if self.overlap else None
+        self.side2 = torch.cuda.Stream(device=dev) if self.overlap else None
+        self._prepared = None
         self.part = None
         self.last_n_unique = self.uq.n_unique
         passes1 = min((self.key_bits + 7) // 8, (self.field_bits + 7) // 8) if self.field_bits else (self.key_bits + 7) // 8
@@ -204,14 +211,25 @@ class SlotShardedStep:
                                     workspace=self.ws_part)
         K.slot_send(self.part.keys, self.part.offsets, b.keys_dst[g], self.limit, b.count_dst[g], b.err, self.N)
 
-    def phase_b(self):
+    def _gather_for(self, s: int):
         b, g = self.buf, self.gen
-        keys = b.own_region(g, "keys")
-        counts = b.own_region(g, "counts")
-        for s in range(self.S):
-            k = keys[s * b.stride:s * b.stride + self.limit]
-            K.gather_keys(self.params.slab, k, self.params._layout_arg, n_dev=counts[s:s + 1],
-                          out=b.remote_rows_slot(s, g, self.limit))
+        k = b.own_region(g, "keys")[s * b.stride:s * b.stride + self.limit]
+        K.gather_keys(self.params.slab, k, self.params._layout_arg, n_dev=b.own_region(g, "counts")[s:s + 1],
+                      out=b.remote_rows_slot(s, g, self.limit))
+
+    def phase_b(self, overlap: bool = False):
+        if not overlap:
+            for s in range(self.S):
+                self._gather_for(s)
+            return
+        cur = torch.cuda.current_stream()
+        self.side2.wait_stream(cur)
+        with torch.cuda.stream(self.side2):
+            for s in range(self.S):
+                if s != self.rank:
+                    self._gather_for(s)
+        self._gather_for(self.rank)
+        cur.wait_stream(self.side2)
 
     def phase_c_expand(self) -> torch.Tensor:
         b, g, uq, part = self.buf, self.gen, self.uq, self.part
@@ -232,6 +250,11 @@ class SlotShardedStep:
         return emb
 
     def phase_d(self):
+        self.phase_d_prepare()
+        self.phase_d_apply()
+
+    def phase_d_prepare(self):
+        """Needs only the received keys (fence 1): compact, dedup, slot-space order."""
         b, g, uq2 = self.buf, self.gen, self.uq2
         K.slot_compact(b.own_region(g, "keys"), b.own_region(g, "counts"), b.stride, self.limit, self.keys_c,
                        self.map_c, self.n_recv)
@@ -239,6 +262,9 @@ class SlotShardedStep:
                  out=uq2, workspace=self.ws_u2)
         K.remap_index(uq2.order, self.map_c, self.n_recv, out=self.order2)
         K.remap_index(uq2.seg_first, self.map_c, uq2.n_unique, out=self.first2)
+
+    def phase_d_apply(self):
+        b, g, uq2 = self.buf, self.gen, self.uq2
         slotted = K.UniqueResult(uniq=uq2.uniq, inverse=None, counts=None, order=self.order2,
                                  seg_offsets=uq2.seg_offsets, n_unique=uq2.n_unique, n=uq2.n, seg_first=self.first2)
         self.params.apply_gradients(slotted, b.own_region(g, "grads"), uq2.n, self.ws_seg, n_rows=uq2.n)
@@ -249,7 +275,13 @@ class SlotShardedStep:
         """Forward half on a real rank (one process per GPU): emb [B*F, dim].  No host synchronisation."""
         self.phase_a(ids)
         self.buf.fence()
-        self.phase_b()
+        if self.overlap:
+            self.side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.side):
+                self.phase_d_prepare()
+                self._prepared = torch.cuda.Event()
+                self._prepared.record()
+        self.phase_b(self.overlap)
         self.buf.fence()
         return self.phase_c_expand()
 
@@ -257,7 +289,12 @@ class SlotShardedStep:
         """Backward half for the ids of the preceding lookup()."""
         self.phase_c_reduce(grad)
         self.buf.fence()
-        self.phase_d()
+        if self._prepared is not None:
+            torch.cuda.current_stream().wait_event(self._prepared)
+            self._prepared = None
+            self.phase_d_apply()
+        else:
+            self.phase_d()
 
     def run(self, ids: torch.Tensor, grad: torch.Tensor) -> torch.Tensor:
         emb = self.lookup(ids)
