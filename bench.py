@@ -55,8 +55,10 @@ def parse_args():
     ap.add_argument("--force-sharded", action="store_true",
                     help="N=1 only: run the multi-shard code path (dedup/partition/exchange/expand) with S=1")
     ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl", "slots"],
-                    help="N>1: all-to-all-v by NVLink peer writes (CUDA IPC, fused with the producing "
-                         "kernels) or by NCCL; auto = peer up to 4 GPUs, nccl above (measured)")
+                    help="N>1: slots = fixed per-pair slots in peer-mapped buffers, no host round trip, step "
+                         "replayed from CUDA graphs; peer = packed all-to-all-v by NVLink peer writes (CUDA "
+                         "IPC, fused with the producing kernels); nccl = all-to-all-v by NCCL; auto = slots "
+                         "(measured fastest at 2 and 8 GPUs)")
     ap.add_argument("--wire", default="f64", choices=["f64", "f32"],
                     help="element type of exchanged partial gradient sums (N>1).  f64 is the parity-validated "
                          "default; f32 halves the gradient bytes but breaks the 1e-6 tolerance for very hot ids "
@@ -227,7 +229,7 @@ def run_b200_arm(a):
         from easydl_b200.exchange import PeerExchange, SingleExchange, TorchExchange
         wire_dtype = torch.float64 if a.wire == "f64" else torch.float32
         if a.exchange == "auto":
-            a.exchange = "peer" if world <= 4 else "nccl"
+            a.exchange = "slots" if world > 1 else "peer"
         slots = world > 1 and a.exchange == "slots"
         if slots:
             ex = None
