@@ -31,6 +31,23 @@ def _align(n: int, a: int = 256) -> int:
     return (n + a - 1) // a * a
 
 
+def slot_layout(world: int, stride: int, dim: int, wire_bytes: int):
+    """Byte layout of one rank's receive buffer -> (offsets {(gen, region): byte offset}, flags_off,
+    counter_off, err_off, nbytes).  Pure host arithmetic (tested without a GPU)."""
+    row_bytes = {"keys": 8, "rows": dim * 4, "grads": dim * wire_bytes, "counts": 4}
+    offs, off = {}, 0
+    for gen in (0, 1):
+        for r in SlotBuffers.REGIONS:
+            offs[(gen, r)] = off
+            rows = world * stride if r != "counts" else world
+            off += _align(rows * row_bytes[r])
+    flags_off = off                           # [world + 1] int64: arrival values, then the timeout mark
+    counter_off = off + 8 * (world + 1)       # int64 fence round counter
+    err_off = counter_off + 8                 # int32 overflow flag
+    off += _align(8 * (world + 1) + 16, 1024)
+    return offs, flags_off, counter_off, err_off, off, row_bytes
+
+
 class SlotBuffers:
     """One rank's receive buffers: per generation (two, alternated step by step) a keys, a rows
     and a grads region of `world` slots x `stride` rows each plus `world` int32 row counts; then
@@ -44,18 +61,8 @@ class SlotBuffers:
         self.world, self.rank, self.device = int(world), int(rank), torch.device(device)
         self.stride, self.dim, self.wire_dtype = int(stride), int(dim), wire_dtype
         wire_b = 8 if wire_dtype == torch.float64 else 4
-        self.row_bytes = {"keys": 8, "rows": dim * 4, "grads": dim * wire_b, "counts": 4}
-        self.off, off = {}, 0
-        for gen in (0, 1):
-            for r in self.REGIONS:
-                self.off[(gen, r)] = off
-                rows = self.world * self.stride if r != "counts" else self.world
-                off += _align(rows * self.row_bytes[r])
-        self.flags_off = off                  # [world + 1] int64 arrival values, [world + 1] = timeout mark
-        self.counter_off = off + 8 * (self.world + 1)
-        self.err_off = self.counter_off + 8
-        off += _align(8 * (self.world + 1) + 16, 1024)
-        self.nbytes = off
+        (self.off, self.flags_off, self.counter_off, self.err_off, self.nbytes,
+         self.row_bytes) = slot_layout(self.world, self.stride, self.dim, wire_b)
         ptr = C.c_void_p()
         _lib.check(self.lib.edl_peer_alloc(C.byref(ptr), self.nbytes), "edl_peer_alloc")
         self.own_ptr = ptr.value

@@ -125,3 +125,50 @@ def test_adam_lr_t_matches_oracle():
     spec = OptimizerSpec.adam()
     for t in (1, 2, 10, 1000):
         assert np.float32(spec.params(t).lr) == O.adam_lr_t(1e-3, 0.9, 0.999, t)
+
+
+def test_slot_buffer_layout_regions_do_not_overlap():
+    """easydl_b200.slot_step.slot_layout: every region of both generations, the flags, the round
+    counter and the overflow flag are disjoint, aligned, and sized for world x stride rows."""
+    from easydl_b200.slot_step import slot_layout
+    for world, stride, dim, wb in [(1, 7, 4, 8), (2, 1000, 64, 8), (8, 1703936, 64, 8), (6, 333, 128, 4)]:
+        offs, flags_off, counter_off, err_off, nbytes, rb = slot_layout(world, stride, dim, wb)
+        spans = []
+        for (gen, region), o in offs.items():
+            rows = world * stride if region != "counts" else world
+            assert o % 256 == 0
+            spans.append((o, o + rows * rb[region]))
+        spans.append((flags_off, flags_off + 8 * (world + 1)))
+        spans.append((counter_off, counter_off + 8))
+        spans.append((err_off, err_off + 4))
+        spans.sort()
+        for (a0, a1), (b0, b1) in zip(spans[:-1], spans[1:]):
+            assert a1 <= b0
+        assert spans[-1][1] <= nbytes
+        assert rb == {"keys": 8, "rows": dim * 4, "grads": dim * wb, "counts": 4}
+        assert world * stride < 2 ** 31           # slot-space rows are int32
+
+
+def test_slot_round_model_matches_packed_all_to_all():
+    """NumPy model of the slot rounds (what csrc/slots.cu computes): sending partition groups into
+    per-sender slots and compacting them in slot order gives the owner exactly the concatenation, in
+    peer-rank order, that the packed all-to-all-v delivers -- the merge order SPEC A4 fixes."""
+    rng = np.random.default_rng(5)
+    S, stride = 4, 50
+    sent = []                                    # sent[src][dst] = keys src sends to dst
+    for src in range(S):
+        sizes = rng.integers(0, 12, size=S)
+        sent.append([rng.integers(0, 1 << 30, size=int(n), dtype=np.int64) for n in sizes])
+    for dst in range(S):
+        slots = np.full(S * stride, -1, dtype=np.int64)
+        counts = np.zeros(S, dtype=np.int32)
+        for src in range(S):                     # edl_slot_send on every sender
+            k = sent[src][dst]
+            slots[src * stride:src * stride + k.size] = k
+            counts[src] = k.size
+        start = np.concatenate([[0], np.cumsum(counts)])   # edl_slot_compact on the owner
+        keys_c = np.concatenate([slots[s * stride:s * stride + counts[s]] for s in range(S)])
+        map_c = np.concatenate([s * stride + np.arange(counts[s]) for s in range(S)]).astype(np.int64)
+        packed = np.concatenate([sent[src][dst] for src in range(S)])
+        assert np.array_equal(keys_c, packed) and start[-1] == packed.size
+        assert np.array_equal(slots[map_c], packed)        # edl_remap_index: compact -> slot-space rows
