@@ -54,11 +54,12 @@ def parse_args():
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
     ap.add_argument("--force-sharded", action="store_true",
                     help="N=1 only: run the multi-shard code path (dedup/partition/exchange/expand) with S=1")
-    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl", "slots"],
+    ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl", "slots", "slots-pipe"],
                     help="N>1: slots = fixed per-pair slots in peer-mapped buffers, no host round trip, step "
                          "replayed from CUDA graphs; peer = packed all-to-all-v by NVLink peer writes (CUDA "
                          "IPC, fused with the producing kernels); nccl = all-to-all-v by NCCL; auto = slots "
                          "(measured fastest at 2 and 8 GPUs)")
+    ap.add_argument("--lanes", type=int, default=2, help="--exchange slots-pipe: number of table groups")
     ap.add_argument("--wire", default="f64", choices=["f64", "f32"],
                     help="element type of exchanged partial gradient sums (N>1).  f64 is the parity-validated "
                          "default; f32 halves the gradient bytes but breaks the 1e-6 tolerance for very hot ids "
@@ -230,7 +231,7 @@ def run_b200_arm(a):
         wire_dtype = torch.float64 if a.wire == "f64" else torch.float32
         if a.exchange == "auto":
             a.exchange = "slots" if world > 1 else "peer"
-        slots = world > 1 and a.exchange == "slots"
+        slots = world > 1 and a.exchange in ("slots", "slots-pipe")
         if slots:
             ex = None
         elif world == 1:
@@ -242,8 +243,11 @@ def run_b200_arm(a):
             ex = TorchExchange(dist.group.WORLD, dev)
         if slots:
             # fixed per-pair slots, no host round trip: the step is replayed from CUDA graphs below
-            from easydl_b200.slot_step import SlotShardedStep
-            step = SlotShardedStep(params, B, group=dist.group.WORLD, wire_dtype=wire_dtype)
+            from easydl_b200.slot_step import PipelinedSlotStep, SlotShardedStep
+            if a.exchange == "slots-pipe":     # table groups one stage apart (not yet timed on real ranks)
+                step = PipelinedSlotStep(params, B, group=dist.group.WORLD, wire_dtype=wire_dtype, n_lanes=a.lanes)
+            else:
+                step = SlotShardedStep(params, B, group=dist.group.WORLD, wire_dtype=wire_dtype)
         else:
             step = ShardedSparseStep(params, B, ex, wire_dtype=wire_dtype)
 
@@ -270,7 +274,7 @@ def run_b200_arm(a):
     if not sharded and a.optimizer == "adagrad" and not a.no_graph:
         from easydl_b200.step import GraphedStep
         graphed = [GraphedStep(step, ids_dev[i], grad_dev) for i in range(nb)]
-    elif sharded and world > 1 and a.exchange == "slots" and a.optimizer == "adagrad" and not a.no_graph:
+    elif sharded and world > 1 and a.exchange in ("slots", "slots-pipe") and a.optimizer == "adagrad" and not a.no_graph:
         from easydl_b200.slot_step import GraphedSlotStep
         graphed = [GraphedSlotStep(step, ids_dev[i], grad_dev) for i in range(nb)]
 

@@ -129,6 +129,42 @@ k_gather(const float4* __restrict__ src, int D4_rt, RowFn fn, int64_t n, const i
   }
 }
 
+// expand into a window of fields: item i = (sample b, field f of the window) lands at output row
+// b * F + f0 + f, so that several field groups of one [B, F] batch fill one [B * F, dim] array.
+template <int kD4>
+__global__ void __launch_bounds__(kThreads, 8)
+k_expand_window(const float4* __restrict__ src, int D4_rt, const int32_t* __restrict__ index, int64_t n,
+                int Fw, int F, int f0, float4* __restrict__ out) {
+  const int D4 = kD4 > 0 ? kD4 : D4_rt;
+  const int64_t total = n * D4;
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  for (int64_t e0 = (int64_t)blockIdx.x * kThreads + threadIdx.x; e0 < total; e0 += stride * kUnroll) {
+    unsigned r[kUnroll], o[kUnroll];   // float4 offsets; the entry point checks that they fit 32 bits
+    float4 v[kUnroll];
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) {
+      int64_t e = e0 + k * stride;
+      if (e < total) {
+        const unsigned i = (unsigned)(e / D4);
+        const unsigned c = (unsigned)e - i * (unsigned)D4;
+        const unsigned b = i / (unsigned)Fw;
+        r[k] = (unsigned)index[i] * (unsigned)D4 + c;
+        o[k] = (b * (unsigned)F + (unsigned)f0 + (i - b * (unsigned)Fw)) * (unsigned)D4 + c;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) {
+      int64_t e = e0 + k * stride;
+      if (e < total) v[k] = src[r[k]];
+    }
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) {
+      int64_t e = e0 + k * stride;
+      if (e < total) edl_st_cs(out + o[k], v[k]);
+    }
+  }
+}
+
 // scatter form: out[pos[i]] = rows[i]
 template <int kD4>
 __global__ void __launch_bounds__(kThreads)
@@ -234,6 +270,34 @@ extern "C" int edl_expand(const float* rows, int dim, const int32_t* index, int6
   IndexRowFn fn{index};
   return launch_gather<IndexRowFn, false>(rows, dim, fn, n, nullptr, nullptr, out, (cudaStream_t)stream,
                                           "edl_expand");
+}
+
+extern "C" int edl_expand_window(const float* rows, int dim, const int32_t* index, int64_t n,
+                                 int fields_in_window, int fields_total, int field0, float* out,
+                                 edl_stream_t stream) {
+  EDL_REQUIRE(dim > 0 && dim % 4 == 0, EDL_EINVAL, "edl_expand_window: dim=%d must be a positive multiple of 4", dim);
+  EDL_REQUIRE(n >= 0, EDL_EINVAL, "edl_expand_window: n negative");
+  EDL_REQUIRE(fields_in_window > 0 && field0 >= 0 && field0 + fields_in_window <= fields_total, EDL_EINVAL,
+              "edl_expand_window: window [%d, %d) does not fit %d fields", field0, field0 + fields_in_window,
+              fields_total);
+  EDL_REQUIRE(n % fields_in_window == 0, EDL_EINVAL, "edl_expand_window: n=%lld is not a multiple of the window's %d fields",
+              (long long)n, fields_in_window);
+  if (n == 0) return EDL_OK;
+  EDL_REQUIRE((n / fields_in_window) * fields_total * (dim / 4) < (int64_t)0xffffffff, EDL_ELIMIT,
+              "edl_expand_window: output larger than 2^32 float4 (n=%lld)", (long long)n);
+  EDL_REQUIRE(rows && index && out, EDL_EINVAL, "edl_expand_window: null pointer");
+  EDL_REQUIRE((((uintptr_t)rows | (uintptr_t)out) & 15) == 0, EDL_EINVAL, "edl_expand_window: rows must be 16-byte aligned");
+  const int D4 = dim / 4;
+  const int g = grid_for(n * D4, kUnroll);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (D4) {
+#define EDL_CASE(W) case W: k_expand_window<W><<<g, kThreads, 0, st>>>((const float4*)rows, D4, index, n, fields_in_window, fields_total, field0, (float4*)out); break;
+    EDL_CASE(4) EDL_CASE(8) EDL_CASE(16) EDL_CASE(32) EDL_CASE(64)
+#undef EDL_CASE
+    default: k_expand_window<0><<<g, kThreads, 0, st>>>((const float4*)rows, D4, index, n, fields_in_window, fields_total, field0, (float4*)out);
+  }
+  EDL_LAUNCH_CHECK("k_expand_window");
+  return EDL_OK;
 }
 
 extern "C" int edl_compose_index(const int32_t* index, const int32_t* map, int64_t n, int32_t* out,

@@ -183,6 +183,23 @@ def expand(rows: torch.Tensor, index: torch.Tensor, *, out: Optional[torch.Tenso
     return out
 
 
+def expand_window(rows: torch.Tensor, index: torch.Tensor, fields_in_window: int, fields_total: int, field0: int,
+                  out: torch.Tensor):
+    """out[(i // Fw) * F + field0 + i % Fw] = rows[index[i]]: one field group of a [B, F] batch."""
+    lib = _lib.load()
+    _need(rows, torch.float32, "rows")
+    _need(index, torch.int32, "index")
+    _need(out, torch.float32, "out")
+    n, dim = index.numel(), rows.shape[1]
+    if out.numel() < (n // max(fields_in_window, 1)) * fields_total * dim:
+        raise ValueError("expand_window: out is smaller than [n / fields_in_window * fields_total, dim]")
+    if rows.numel() // 4 >= 1 << 32:
+        raise ValueError("expand_window: rows larger than 2^32 float4")
+    check(lib.edl_expand_window(_ptr(rows), dim, _ptr(index), n, fields_in_window, fields_total, field0, _ptr(out),
+                                _stream()), "edl_expand_window")
+    return out
+
+
 def compose_index(index: torch.Tensor, mapping: torch.Tensor):
     lib = _lib.load()
     _need(index, torch.int32, "index")

@@ -88,9 +88,11 @@ class ShardParameters:
 
     # ------------------------------------------------------------------ A4 + A5
     def apply_gradients(self, uq: K.UniqueResult, grad: torch.Tensor, max_unique: Optional[int] = None,
-                        workspace=None, n_rows: Optional[int] = None):
-        """Segment-sum grad rows per unique key and run the optimizer on the touched rows."""
-        self.step += 1
+                        workspace=None, n_rows: Optional[int] = None, bump_step: bool = True):
+        """Segment-sum grad rows per unique key and run the optimizer on the touched rows.
+        bump_step=False: a further part of the same training step (disjoint ids), same step number."""
+        if bump_step:
+            self.step += 1
         slot1 = self.slots[1] if len(self.slots) > 1 else None
         K.segreduce_update(self.slab, self.slots[0], slot1, uq.uniq, uq.order, uq.seg_offsets,
                            uq.n_unique, uq.n if max_unique is None else max_unique, grad,

@@ -152,10 +152,16 @@ class SlotShardedStep:
 
     def __init__(self, params: ShardParameters, batch_size: int, buffers: Optional[SlotBuffers] = None, *,
                  group=None, n_fields: Optional[int] = None, wire_dtype=torch.float64,
-                 slot_slack: float = 1.5):
+                 slot_slack: float = 1.5, field_range=None, emb: Optional[torch.Tensor] = None):
+        # field_range = (f0, f1): this object handles only fields f0..f1-1 of a [B, F_total] batch (one
+        # lane of PipelinedSlotStep): its ids are the contiguous [B, f1 - f0] slice, its embeddings go
+        # to rows b * F_total + f of the shared `emb`, its gradient rows are read from there too.
         self.params = params
         self.S, self.rank = params.num_shards, params.shard
-        self.F = params.layout.n_tables if n_fields is None else n_fields
+        self.F_total = params.layout.n_tables if n_fields is None else n_fields
+        self.f0, f1 = (0, self.F_total) if field_range is None else field_range
+        self.F = f1 - self.f0
+        self.windowed = self.F != self.F_total
         self.B = int(batch_size)
         self.N = self.B * self.F
         self.dim, self.wire_dtype = params.dim, wire_dtype
@@ -168,7 +174,7 @@ class SlotShardedStep:
                 buffers.connect_ipc(group)
         self.buf = buffers
         self.gen = 0
-        self.field_base = torch.from_numpy(params.layout.key_base[:self.F].copy()).to(dev)
+        self.field_base = torch.from_numpy(params.layout.key_base[self.f0:self.f0 + self.F].copy()).to(dev)
         self.key_bits, self.field_bits = params.layout.key_bits, params.layout.field_bits
         lib = _lib.load()
         N, R = self.N, self.S * self.limit
@@ -187,12 +193,20 @@ class SlotShardedStep:
         self.order2 = torch.empty(R, **i32)
         self.first2 = torch.empty(R, **i32)
         self.slotpos = torch.empty(N, **i32)
-        self.emb = torch.empty((N, self.dim), dtype=torch.float32, device=dev)
+        if emb is None:
+            emb = torch.empty((self.B * self.F_total, self.dim), dtype=torch.float32, device=dev)
+        self.emb = emb
+        if self.windowed:
+            j = torch.arange(N, dtype=torch.int64, device=dev)
+            self.grad_map = ((j // self.F) * self.F_total + self.f0 + j % self.F).to(torch.int32)
+            self.order_w = torch.empty(N, **i32)     # order / seg_first as rows of the full [B * F_total] batch
+            self.first_w = torch.empty(N, **i32)
         self.ws_u1 = torch.empty(lib.edl_unique_workspace_bytes(N, self.key_bits, self.F, self.field_bits),
                                  dtype=torch.uint8, device=dev)
         self.ws_u2 = torch.empty(lib.edl_unique_workspace_bytes(R, self.key_bits, 0, 0), dtype=torch.uint8, device=dev)
         self.ws_part = torch.empty(lib.edl_partition_mod_workspace_bytes(N, self.S), dtype=torch.uint8, device=dev)
-        self.ws_seg = torch.empty(max(lib.edl_segreduce_workspace_bytes(N, N, self.dim),
+        n_grad = self.B * self.F_total
+        self.ws_seg = torch.empty(max(lib.edl_segreduce_workspace_bytes(N, n_grad, self.dim),
                                       lib.edl_segreduce_workspace_bytes(R, R, self.dim)), dtype=torch.uint8, device=dev)
         self.S_const = torch.tensor([self.S], dtype=torch.int64, device=dev)
         # helper streams (real ranks): the owner-side dedup of the received keys runs beside the rest
@@ -217,6 +231,9 @@ class SlotShardedStep:
         self.part = K.partition_mod(self.uq.uniq, self.params.layout_dev, self.S, n_dev=self.uq.n_unique,
                                     workspace=self.ws_part)
         K.slot_send(self.part.keys, self.part.offsets, b.keys_dst[g], self.limit, b.count_dst[g], b.err, self.N)
+        if self.windowed:
+            K.remap_index(self.uq.order, self.grad_map, None, out=self.order_w)
+            K.remap_index(self.uq.seg_first, self.grad_map, self.uq.n_unique, out=self.first_w)
 
     def _gather_for(self, s: int):
         b, g = self.buf, self.gen
@@ -242,13 +259,17 @@ class SlotShardedStep:
         b, g, uq, part = self.buf, self.gen, self.uq, self.part
         K.slot_positions(part.pos, uq.n_unique, part.offsets, b.stride, out=self.slotpos)
         idx = K.compose_index(uq.inverse, self.slotpos)
-        K.expand(b.own_region(g, "rows"), idx, out=self.emb)
+        if self.windowed:
+            K.expand_window(b.own_region(g, "rows"), idx, self.F, self.F_total, self.f0, out=self.emb)
+        else:
+            K.expand(b.own_region(g, "rows"), idx, out=self.emb)
         return self.emb
 
     def phase_c_reduce(self, grad: torch.Tensor):
         b, g, uq, part = self.buf, self.gen, self.uq, self.part
         table = torch.cat([self.S_const, part.offsets.to(torch.int64), b.grads_dst[g]])
-        K.segreduce(grad, uq.order, uq.seg_offsets, uq.n_unique, self.N, seg_first=uq.seg_first, out_pos=part.pos,
+        order, first = (self.order_w, self.first_w) if self.windowed else (uq.order, uq.seg_first)
+        K.segreduce(grad, order, uq.seg_offsets, uq.n_unique, self.N, seg_first=first, out_pos=part.pos,
                     out=None, out_dtype=self.wire_dtype, dst_table=table, workspace=self.ws_seg)
 
     def phase_c(self, grad: torch.Tensor) -> torch.Tensor:
@@ -256,9 +277,9 @@ class SlotShardedStep:
         self.phase_c_reduce(grad)
         return emb
 
-    def phase_d(self):
+    def phase_d(self, bump_step: bool = True):
         self.phase_d_prepare()
-        self.phase_d_apply()
+        self.phase_d_apply(bump_step)
 
     def phase_d_prepare(self):
         """Needs only the received keys (fence 1): compact, dedup, slot-space order."""
@@ -270,11 +291,12 @@ class SlotShardedStep:
         K.remap_index(uq2.order, self.map_c, self.n_recv, out=self.order2)
         K.remap_index(uq2.seg_first, self.map_c, uq2.n_unique, out=self.first2)
 
-    def phase_d_apply(self):
+    def phase_d_apply(self, bump_step: bool = True):
         b, g, uq2 = self.buf, self.gen, self.uq2
         slotted = K.UniqueResult(uniq=uq2.uniq, inverse=None, counts=None, order=self.order2,
                                  seg_offsets=uq2.seg_offsets, n_unique=uq2.n_unique, n=uq2.n, seg_first=self.first2)
-        self.params.apply_gradients(slotted, b.own_region(g, "grads"), uq2.n, self.ws_seg, n_rows=uq2.n)
+        self.params.apply_gradients(slotted, b.own_region(g, "grads"), uq2.n, self.ws_seg, n_rows=uq2.n,
+                                    bump_step=bump_step)
         self.gen ^= 1
 
     # ------------------------------------------------------------------ drivers
@@ -367,3 +389,152 @@ class GraphedSlotStep:
         st.gen ^= 1
         st.params.step += 1
         return st.emb
+
+
+class PipelinedSlotStep:
+    """SlotShardedStep cut into `n_lanes` groups of tables that move through the exchange rounds one
+    stage apart, so that a lane's NVLink-bound round (gather into the peers, reduce into the owners)
+    runs beside another lane's HBM-bound work (dedup, expand, optimizer).  Tables never share rows, so
+    the lanes are independent and the result is bit-identical to the unpipelined step.
+
+        forward   stage t: lane t dedup + send keys | lane t-1 owner gather | lane t-2 expand     | fence
+        backward  stage t: lane t reduce into the owners | lane t-1 owner reduce + optimizer       | fence
+
+    One fence per stage closes every round of that stage; the fences are issued on the calling stream
+    in a fixed order on every rank.  [status: parity on virtual ranks; not yet timed on real ranks]"""
+
+    def __init__(self, params: ShardParameters, batch_size: int, *, group=None, buffers=None, n_lanes: int = 2,
+                 wire_dtype=torch.float64, slot_slack: float = 1.5):
+        self.params = params
+        self.S, self.rank = params.num_shards, params.shard
+        self.F = params.layout.n_tables
+        self.B = int(batch_size)
+        self.N = self.B * self.F
+        self.dim = params.dim
+        dev = params.device
+        self.device = dev
+        if not 1 <= n_lanes <= self.F:
+            raise ValueError("n_lanes must be between 1 and the number of tables")
+        cuts = [self.F * g // n_lanes for g in range(n_lanes + 1)]
+        self.emb = torch.empty((self.N, self.dim), dtype=torch.float32, device=dev)
+        self.lanes: List[SlotShardedStep] = []
+        for g in range(n_lanes):
+            self.lanes.append(SlotShardedStep(params, batch_size, None if buffers is None else buffers[g], group=group,
+                                              wire_dtype=wire_dtype, slot_slack=slot_slack,
+                                              field_range=(cuts[g], cuts[g + 1]), emb=self.emb))
+        self.cuts = cuts
+        self.streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
+        self.prep = torch.cuda.Stream(device=dev, priority=-1)
+        self._prepared = [None] * n_lanes
+        self.last_n_unique = self.lanes[0].uq.n_unique
+        self.launches_per_step = sum(l.launches_per_step for l in self.lanes) + n_lanes
+
+    # the buffer generation is per lane but always equal across lanes (GraphedSlotStep reads / sets it)
+    @property
+    def gen(self) -> int:
+        return self.lanes[0].gen
+
+    @gen.setter
+    def gen(self, v: int):
+        for l in self.lanes:
+            l.gen = v
+
+    def _lane_ids(self, ids: torch.Tensor):
+        ids = ids.view(self.B, self.F)
+        return [ids[:, a:b].contiguous() for a, b in zip(self.cuts[:-1], self.cuts[1:])]
+
+    # ---- stage contents (shared by the real and the virtual driver)
+    def _forward_stage(self, t: int, lane_ids):
+        """[(callable, kind)] of forward stage t; kind "link" = NVLink-bound, "hbm" otherwise."""
+        G, ops = len(self.lanes), []
+        if 0 <= t - 1 < G:
+            ops.append((lambda l=self.lanes[t - 1]: l.phase_b(l.overlap and self._real), "link"))
+        if 0 <= t < G:
+            ops.append((lambda l=self.lanes[t], i=lane_ids[t]: l.phase_a(i), "hbm"))
+        if 0 <= t - 2 < G:
+            ops.append((lambda l=self.lanes[t - 2]: l.phase_c_expand(), "hbm"))
+        return ops
+
+    def _backward_stage(self, t: int, grad):
+        G, ops = len(self.lanes), []
+        if 0 <= t < G:
+            ops.append((lambda l=self.lanes[t]: l.phase_c_reduce(grad), "link"))
+        if 0 <= t - 1 < G:
+            ops.append((lambda k=t - 1: self._apply(k), "hbm"))
+        return ops
+
+    def _apply(self, k: int):
+        lane = self.lanes[k]
+        if self._prepared[k] is not None:
+            torch.cuda.current_stream().wait_event(self._prepared[k])
+            self._prepared[k] = None
+            lane.phase_d_apply(bump_step=(k == 0))
+        else:
+            lane.phase_d(bump_step=(k == 0))
+
+    def _run_stage(self, ops):
+        """First op on the calling stream, the others on helper streams, all joined before returning."""
+        cur = torch.cuda.current_stream()
+        for j, (fn, _) in enumerate(ops[1:]):
+            st = self.streams[j % len(self.streams)]
+            st.wait_stream(cur)
+            with torch.cuda.stream(st):
+                fn()
+        if ops:
+            ops[0][0]()
+        for j in range(min(len(ops) - 1, len(self.streams))):
+            cur.wait_stream(self.streams[j])
+
+    # ---- real ranks
+    _real = True
+
+    def lookup(self, ids: torch.Tensor) -> torch.Tensor:
+        lane_ids = self._lane_ids(ids)
+        G = len(self.lanes)
+        for t in range(G + 2):
+            if 1 <= t <= G:       # lane t-1's keys arrived with the previous fence: start its owner-side dedup
+                self.prep.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(self.prep):
+                    self.lanes[t - 1].phase_d_prepare()
+                    ev = torch.cuda.Event()
+                    ev.record()
+                self._prepared[t - 1] = ev
+            self._run_stage(self._forward_stage(t, lane_ids))
+            if t < G + 1:
+                self.lanes[0].buf.fence()
+        return self.emb
+
+    def update(self, ids: Optional[torch.Tensor], grad: torch.Tensor, uq=None):
+        G = len(self.lanes)
+        for t in range(G + 1):
+            self._run_stage(self._backward_stage(t, grad))
+            if t < G:
+                self.lanes[0].buf.fence()
+
+    def run(self, ids: torch.Tensor, grad: torch.Tensor) -> torch.Tensor:
+        emb = self.lookup(ids)
+        self.update(ids, grad)
+        return emb
+
+    def check(self):
+        for l in self.lanes:
+            l.check()
+
+
+def run_virtual_pipelined(steps: Sequence[PipelinedSlotStep], ids: Sequence[torch.Tensor],
+                          grads: Sequence[torch.Tensor]):
+    """PipelinedSlotStep for all ranks as virtual ranks on one GPU and one stream (tests): stage by
+    stage over the ranks, no fences, no helper streams."""
+    G = len(steps[0].lanes)
+    lane_ids = [st._lane_ids(i) for st, i in zip(steps, ids)]
+    for st in steps:
+        st._real = False
+    for t in range(G + 2):
+        for st, li in zip(steps, lane_ids):
+            for fn, _ in st._forward_stage(t, li):
+                fn()
+    for t in range(G + 1):
+        for st, g in zip(steps, grads):
+            for fn, _ in st._backward_stage(t, g):
+                fn()
+    return [st.emb for st in steps]

@@ -136,6 +136,12 @@ int edl_gather_ids(const float* slab, int dim, const int64_t* ids, int64_t n,
                    const int64_t* field_base, int n_fields, float* out, edl_stream_t stream);
 int edl_expand(const float* rows, int dim, const int32_t* index, int64_t n, float* out,
                edl_stream_t stream);
+/* edl_expand into a window of fields of a [B, fields_total] batch: item i (sample i / fields_in_window,
+ * field i % fields_in_window of the window) lands at output row
+ * (i / fields_in_window) * fields_total + field0 + i % fields_in_window.  Lets several field groups,
+ * looked up one after the other (pipelined exchange rounds), fill one [B * fields_total, dim] array. */
+int edl_expand_window(const float* rows, int dim, const int32_t* index, int64_t n, int fields_in_window,
+                      int fields_total, int field0, float* out, edl_stream_t stream);
 /* index2 composition for the sharded path: out[j] = map[index[j]] (int32) */
 int edl_compose_index(const int32_t* index, const int32_t* map, int64_t n, int32_t* out,
                       edl_stream_t stream);

@@ -161,3 +161,69 @@ def test_slot_overflow_is_reported(cuda):
         st[0].check()
     for b in bufs:
         b.close()
+
+
+def test_expand_window(cuda):
+    from easydl_b200 import kernels as K
+    rng = np.random.default_rng(2)
+    B, F, Fw, f0, dim, R = 37, 7, 3, 2, 16, 50
+    rows = rng.standard_normal((R, dim)).astype(np.float32)
+    idx = rng.integers(0, R, size=B * Fw).astype(np.int32)
+    out = torch.full((B * F, dim), -1.0, dtype=torch.float32, device=cuda)
+    K.expand_window(dev(rows, cuda), dev(idx, cuda), Fw, F, f0, out)
+    want = np.full((B, F, dim), -1.0, dtype=np.float32)
+    want[:, f0:f0 + Fw, :] = rows[idx].reshape(B, Fw, dim)
+    assert np.array_equal(out.cpu().numpy().reshape(B, F, dim), want)
+
+
+def _virtual_pipelined(cuda, rows, dim, S, opt_name, batch, n_lanes):
+    from easydl_b200.optimizer import OptimizerSpec
+    from easydl_b200.parameters import ShardParameters
+    from easydl_b200.slot_step import PipelinedSlotStep, SlotBuffers
+    po = OptimizerSpec.adagrad() if opt_name == "adagrad" else OptimizerSpec.adam()
+    params = [ShardParameters(rows, dim, po, S, s, device=cuda) for s in range(S)]
+    F = len(rows)
+    cuts = [F * g // n_lanes for g in range(n_lanes + 1)]
+    bufs = []                                     # bufs[lane][rank]
+    for g in range(n_lanes):
+        lane = [SlotBuffers(S, s, cuda, batch * (cuts[g + 1] - cuts[g]), dim) for s in range(S)]
+        for b in lane:
+            b.connect_local(lane)
+        bufs.append(lane)
+    steps = [PipelinedSlotStep(params[s], batch, buffers=[bufs[g][s] for g in range(n_lanes)], n_lanes=n_lanes)
+             for s in range(S)]
+    return params, bufs, steps
+
+
+@pytest.mark.parametrize("S,opt,n_lanes", [(2, "adagrad", 2), (4, "adam", 3), (3, "adagrad", 5)])
+def test_pipelined_slot_step_same_bits_as_unpipelined_and_oracle(cuda, S, opt, n_lanes):
+    from easydl_b200.slot_step import run_virtual, run_virtual_pipelined
+    from test_gpu_sharded import _compare_state
+    rows, dim, batch, steps = [5000, 301, 70001, 11, 6], 32, 512, 3
+    params, bufs, st = _virtual_pipelined(cuda, rows, dim, S, opt, batch, n_lanes)
+    ref_p, ref_b, ref_st = _virtual(cuda, rows, dim, S, opt, batch)
+    oo = O.OptimizerSpec.adagrad() if opt == "adagrad" else O.OptimizerSpec.adam()
+    osh = [O.OracleShard(rows, dim, oo, S, s) for s in range(S)]
+    bases = O.key_bases(rows)
+    for k in range(steps):
+        kw, gw, di, dg = [], [], [], []
+        for r in range(S):
+            _, ids, _ = O.criteo_batch(rows, batch, 1.05, step=k * 8 + r)
+            g = O.synthetic_grad(ids.size, dim, step=k * 8 + r)
+            kw.append(O.fuse_keys(ids, bases)); gw.append(g)
+            di.append(dev(ids, cuda)); dg.append(dev(g, cuda))
+        embs = run_virtual_pipelined(st, di, dg)
+        ref = run_virtual(ref_st, di, dg)
+        O.sharded_step(osh, kw, gw)
+        for a, b in zip(embs, ref):
+            assert torch.equal(a, b), f"emb step {k}"
+    for s in st:
+        s.check()
+    for p, q in zip(params, ref_p):
+        assert p.step == q.step and torch.equal(p.slab, q.slab) and torch.equal(p.slots[0], q.slots[0])
+    _compare_state(cuda, params, osh, oo.n_slots)
+    for lane in bufs:
+        for b in lane:
+            b.close()
+    for b in ref_b:
+        b.close()

@@ -1,7 +1,7 @@
 """Multi-GPU parity + timing of the sharded step on real ranks (torchrun, one rank per GPU):
 every rank runs K steps through NCCL (TorchExchange) or peer writes (PeerExchange) and the final
 shard state is compared with the oracle's global float64 pass.  Small tables so the oracle is quick.
-  torchrun --nproc-per-node N tools/mgpu_check.py [peer|nccl|slots|slots-graph] [adam|adagrad]"""
+  torchrun --nproc-per-node N tools/mgpu_check.py [peer|nccl|slots|slots-graph|pipe|pipe-graph] [adam|adagrad]"""
 import os, sys, time, numpy as np, torch, torch.distributed as dist
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from easydl_b200.exchange import PeerExchange, TorchExchange
@@ -19,10 +19,11 @@ rows, D, B, K = [50_000, 301, 700_001, 11, 6, 90_000], 32, 4096, 3
 po = OptimizerSpec.adam() if opt_name == "adam" else OptimizerSpec.adagrad()
 oo = O.OptimizerSpec.adam() if opt_name == "adam" else O.OptimizerSpec.adagrad()
 P = ShardParameters(rows, D, po, world, rank, device=dev)
-if mode.startswith("slots"):
-    from easydl_b200.slot_step import GraphedSlotStep, SlotShardedStep
+if mode.startswith("slots") or mode.startswith("pipe"):
+    from easydl_b200.slot_step import GraphedSlotStep, PipelinedSlotStep, SlotShardedStep
     ex = None
-    st = SlotShardedStep(P, B, group=dist.group.WORLD)
+    Step = PipelinedSlotStep if mode.startswith("pipe") else SlotShardedStep
+    st = Step(P, B, group=dist.group.WORLD)
 else:
     ex = PeerExchange(dist.group.WORLD, dev, 2 * B * len(rows), D) if mode == "peer" else TorchExchange(dist.group.WORLD, dev)
     st = ShardedSparseStep(P, B, ex)
@@ -33,7 +34,7 @@ for k in range(K):
     g = O.synthetic_grad(ids.size, D, step=k * world + rank)
     embs.append(st.run(torch.from_numpy(ids).to(dev), torch.from_numpy(g).to(dev)).cpu().numpy())
 torch.cuda.synchronize()
-if mode.startswith("slots"):
+if mode.startswith("slots") or mode.startswith("pipe"):
     st.check()
 # oracle (every rank recomputes the global pass; cheap at this size)
 osh = [O.OracleShard(rows, D, oo, world, s) for s in range(world)]
@@ -54,23 +55,23 @@ for got, want in [(rec.rows.numpy(), osh[rank].w)] + [(rec.slots[i].numpy(), osh
 flag = torch.tensor([1 if ok else 0], device=dev); dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if rank == 0:
     print(f"[{mode}/{opt_name}] world={world} parity vs oracle: {'OK' if int(flag.item()) else 'FAIL'}")
-if mode == "slots-graph":
+if mode in ("slots-graph", "pipe-graph"):
     # graph replay on top of the checked state: K more steps replayed == K more steps issued eagerly
     ids_d, g_d = torch.from_numpy(ids).to(dev), torch.from_numpy(g).to(dev)
     P2 = ShardParameters(rows, D, po, world, rank, device=dev)
-    st2 = SlotShardedStep(P2, B, group=dist.group.WORLD)
+    st2 = Step(P2, B, group=dist.group.WORLD)
     for _ in range(4):
         st2.run(ids_d, g_d)
     st2.check()
     P3 = ShardParameters(rows, D, po, world, rank, device=dev)
-    st3 = SlotShardedStep(P3, B, group=dist.group.WORLD)
+    st3 = Step(P3, B, group=dist.group.WORLD)
     gs = GraphedSlotStep(st3, ids_d, g_d)          # two eager warm-up steps inside
     gs.run(); gs.run()
     st3.check()
     same = torch.equal(P2.slab, P3.slab) and torch.equal(P2.slots[0], P3.slots[0]) and P2.step == P3.step
     f2 = torch.tensor([1 if same else 0], device=dev); dist.all_reduce(f2, op=dist.ReduceOp.MIN)
     if rank == 0:
-        print(f"[slots-graph] graph replay == eager: {'OK' if int(f2.item()) else 'FAIL'}")
+        print(f"[{mode}] graph replay == eager: {'OK' if int(f2.item()) else 'FAIL'}")
     ok &= bool(int(f2.item()))
 if mode == "peer":
     ex.close()
