@@ -227,3 +227,52 @@ def test_pipelined_slot_step_same_bits_as_unpipelined_and_oracle(cuda, S, opt, n
             b.close()
     for b in ref_b:
         b.close()
+
+
+@pytest.mark.parametrize("n_lanes", [1, 2])
+def test_real_drivers_world_of_one_eager_equals_graph(cuda, n_lanes):
+    """The real-rank drivers (helper streams, fences, CUDA-graph replay with alternating buffer
+    generations) with a world of one: graph replay == eager issue == the phase-by-phase virtual run."""
+    from easydl_b200.optimizer import OptimizerSpec
+    from easydl_b200.parameters import ShardParameters
+    from easydl_b200.slot_step import (GraphedSlotStep, PipelinedSlotStep, SlotBuffers, SlotShardedStep,
+                                       run_virtual)
+    rows, dim, batch = [20000, 3000, 17, 900], 32, 1024
+    F = len(rows)
+    _, ids, _ = O.criteo_batch(rows, batch, 1.1, step=3)
+    d_ids, d_g = dev(ids, cuda), dev(O.synthetic_grad(ids.size, dim, step=3), cuda)
+
+    def make():
+        p = ShardParameters(rows, dim, OptimizerSpec.adagrad(), 1, 0, device=cuda)
+        if n_lanes == 1:
+            b = SlotBuffers(1, 0, cuda, batch * F, dim)
+            b.connect_local([b])
+            return p, [b], SlotShardedStep(p, batch, b)
+        cuts = [F * g // n_lanes for g in range(n_lanes + 1)]
+        bs = [SlotBuffers(1, 0, cuda, batch * (cuts[g + 1] - cuts[g]), dim) for g in range(n_lanes)]
+        for b in bs:
+            b.connect_local([b])
+        return p, bs, PipelinedSlotStep(p, batch, buffers=bs, n_lanes=n_lanes)
+
+    p1, b1, eager = make()
+    for _ in range(4):
+        emb_e = eager.run(d_ids, d_g).clone()
+    eager.check()
+    p2, b2, st2 = make()
+    graphed = GraphedSlotStep(st2, d_ids, d_g)       # two eager steps inside
+    graphed.run()
+    emb_g = graphed.run().clone()
+    st2.check()
+    assert p1.step == p2.step == 4
+    assert torch.equal(emb_e, emb_g)
+    assert torch.equal(p1.slab, p2.slab) and torch.equal(p1.slots[0], p2.slots[0])
+    # the unpipelined phase-by-phase run gives the same bits
+    p3 = ShardParameters(rows, dim, OptimizerSpec.adagrad(), 1, 0, device=cuda)
+    b3 = SlotBuffers(1, 0, cuda, batch * F, dim)
+    b3.connect_local([b3])
+    st3 = SlotShardedStep(p3, batch, b3)
+    for _ in range(4):
+        run_virtual([st3], [d_ids], [d_g])
+    assert torch.equal(p1.slab, p3.slab) and torch.equal(p1.slots[0], p3.slots[0])
+    for b in b1 + b2 + [b3]:
+        b.close()
