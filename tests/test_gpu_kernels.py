@@ -393,3 +393,20 @@ print("DIGEST", h.hexdigest())
         assert out.returncode == 0, out.stderr[-2000:]
         digests.append([l for l in out.stdout.splitlines() if l.startswith("DIGEST")][0])
     assert len(set(digests)) == 1, digests
+
+
+def test_c_host_program(cuda, tmp_path):
+    """examples/c_host.c: dedup + segmented reduce + Adagrad from a plain C program (cudaMalloc'ed
+    buffers, no Python in the process), checked inside the program against host arithmetic."""
+    import os, subprocess
+    from test_host import _c_host_cmd
+    exe = str(tmp_path / "c_host")
+    root, cmd = _c_host_cmd(exe)
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    cuda_home = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    env = dict(os.environ, LD_LIBRARY_PATH=os.pathsep.join(
+        [os.path.join(root, "easydl_b200"), os.path.join(cuda_home, "lib64"), os.environ.get("LD_LIBRARY_PATH", "")]))
+    r = subprocess.run([exe], capture_output=True, text=True, env=env, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "mismatching elements: 0" in r.stdout

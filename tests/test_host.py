@@ -172,3 +172,26 @@ def test_slot_round_model_matches_packed_all_to_all():
         packed = np.concatenate([sent[src][dst] for src in range(S)])
         assert np.array_equal(keys_c, packed) and start[-1] == packed.size
         assert np.array_equal(slots[map_c], packed)        # edl_remap_index: compact -> slot-space rows
+
+
+def _c_host_cmd(out):
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    return root, ["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(root, "include"), "-I",
+                  os.path.join(cuda, "include"), os.path.join(root, "examples", "c_host.c"), "-L",
+                  os.path.join(root, "easydl_b200"), "-ledlsparse", "-L", os.path.join(cuda, "lib64"), "-lcudart",
+                  "-lm", "-o", out]
+
+
+def test_header_is_plain_c_and_c_host_links(tmp_path):
+    """include/edlsparse.h compiles as C99 (no C++ in the boundary) and a C program using it links
+    against libedlsparse.so without anything from Python or torch."""
+    import os, subprocess
+    root, cmd = _c_host_cmd(str(tmp_path / "c_host"))
+    r = subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-fsyntax-only", "-x", "c",
+                        os.path.join(root, "include", "edlsparse.h")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert os.path.exists(tmp_path / "c_host")
