@@ -169,6 +169,10 @@ k_seg_classify(const int32_t* __restrict__ seg, const int32_t* __restrict__ n_un
 // therefore must not be inside a stream capture).  The mutex keeps one call's record/wait pairs
 // on the shared events together when several host threads drive one device.
 struct ForkRes { cudaStream_t side; cudaEvent_t fork, join; bool ready; };
+inline std::mutex& fork_mutex() {   // one for every instantiation of launch_direct
+  static std::mutex mu;
+  return mu;
+}
 inline int fork_res(ForkRes** out) {
   static ForkRes res[64];
   int dev = 0;
@@ -354,8 +358,7 @@ int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t*
   // k_seg_direct (their latency tail hides under it); 0: the three kernels in a row on `st`.
   static int fork = -1;
   if (fork < 0) { const char* e = getenv("EDL_SEG_FORK"); fork = e ? atoi(e) : kForkDefault; }
-  static std::mutex fork_mu;
-  std::unique_lock<std::mutex> lock(fork_mu, std::defer_lock);
+  std::unique_lock<std::mutex> lock(fork_mutex(), std::defer_lock);
   ForkRes* F = nullptr;
   cudaStream_t st_hot = st;
   int32_t* reg_counters = W.counters;
