@@ -271,7 +271,7 @@ def run_b200_arm(a):
     # S == 1, Adagrad: the step is replayed from CUDA graphs (one per id batch buffer), which
     # removes the host launch gaps between its 17 kernels.  Otherwise: eager launches.
     graphed = None
-    if not sharded and a.optimizer == "adagrad" and not a.no_graph:
+    if not sharded and not a.no_graph:
         from easydl_b200.step import GraphedStep
         graphed = [GraphedStep(step, ids_dev[i], grad_dev) for i in range(nb)]
     elif sharded and world > 1 and a.exchange in ("slots", "slots-pipe") and a.optimizer == "adagrad" and not a.no_graph:
@@ -333,6 +333,7 @@ def run_b200_arm(a):
                 ev[i][1].record()
                 graphed[j].g_dedup.replay()
                 ev[i][2].record()
+                params.stage_rate(params.step + 1)
                 graphed[j].g_update.replay()
                 params.step += 1
             else:

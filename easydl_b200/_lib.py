@@ -22,7 +22,7 @@ class EdlError(RuntimeError):
 
 class OptParams(C.Structure):
     _fields_ = [("kind", C.c_int), ("lr", C.c_float), ("eps", C.c_float),
-                ("beta1", C.c_float), ("beta2", C.c_float)]
+                ("beta1", C.c_float), ("beta2", C.c_float), ("lr_dev", C.c_void_p)]
 
 
 _p = C.c_void_p
@@ -34,6 +34,8 @@ _int = C.c_int
 PROTOTYPES = {
     "edl_version": (_int, []),
     "edl_last_error_string": (C.c_char_p, []),
+    "edl_tuning_set": (_int, [C.c_char_p, _int]),
+    "edl_tuning_get": (_int, [C.c_char_p, C.POINTER(C.c_int)]),
     "edl_init_rows": (_int, [_p, _int, _p, _i64, _i64, C.c_uint64, _p]),
     "edl_fill_f32": (_int, [_p, _i64, C.c_float, _p]),
     "edl_unique_workspace_bytes": (_sz, [_i64, _int, _int, _int]),
@@ -95,6 +97,17 @@ def load() -> C.CDLL:
         fn.argtypes = args
     _lib = lib
     return lib
+
+
+def tuning_set(name: str, value: int):
+    """Set a launch-shape knob of the library (include/edlsparse.h lists them)."""
+    check(load().edl_tuning_set(name.encode(), int(value)), "edl_tuning_set")
+
+
+def tuning_get(name: str) -> int:
+    v = C.c_int(0)
+    check(load().edl_tuning_get(name.encode(), C.byref(v)), "edl_tuning_get")
+    return int(v.value)
 
 
 def check(rc: int, what: str):

@@ -101,15 +101,27 @@ class CheckpointSaver:
         path = shard_file(self.directory, rec.step, params.shard, params.num_shards)
         write_shard_file(path, params.layout, params.dim, params.opt.kind, rec)
         if self.keep_max > 0 and params.shard == 0:
-            vs = sorted(list_versions(self.directory))
-            for v in vs[:-self.keep_max]:
+            self.prune()
+        return path
+
+    def prune(self):
+        """Keep the newest `keep_max` COMPLETE versions (every shard's file present) and whatever is newer
+        than the oldest of them (versions other shards are still writing).  Shard 0 calls this after its
+        own write without waiting for the others, so an older complete version must survive until a newer
+        one is whole: otherwise a crash of any other shard would leave nothing to restore from."""
+        vs = list_versions(self.directory)
+        complete = [v for v in vs if version_complete(self.directory, v)]
+        if len(complete) <= self.keep_max:
+            return
+        oldest_kept = complete[-self.keep_max]
+        for v in vs:
+            if v < oldest_kept:
                 for p in glob.glob(os.path.join(self.directory, f"version-{v}", "*.ckpt")):
                     os.remove(p)
                 try:
                     os.rmdir(os.path.join(self.directory, f"version-{v}"))
                 except OSError:
                     pass
-        return path
 
 
 def list_versions(directory: str) -> List[int]:
@@ -137,15 +149,31 @@ def version_files(directory: str, version: int) -> List[str]:
     return [p for _, _, p in sorted(parsed)]
 
 
+def version_complete(directory: str, version: int) -> bool:
+    try:
+        version_files(directory, version)
+        return True
+    except (FileNotFoundError, ValueError):
+        return False
+
+
+def latest_complete_version(directory: str) -> int:
+    """Newest version whose shard files are all present (a version that some shard was still writing
+    when the job died is skipped)."""
+    vs = list_versions(directory)
+    for v in reversed(vs):
+        if version_complete(directory, v):
+            return v
+    raise FileNotFoundError(f"no complete checkpoint version in {directory} (versions seen: {vs})")
+
+
 def restore_params_from_checkpoint(directory: str, params: ShardParameters,
                                    version: Optional[int] = None) -> int:
     """Re-initialise `params` (any shard count) and load its rows from ALL shard files of the
-    version; returns the restored step.  This is scale-up / scale-down through checkpoints."""
+    version (default: the newest complete one); returns the restored step.  This is scale-up /
+    scale-down through checkpoints, and the recovery of a failed PS shard."""
     if version is None:
-        vs = list_versions(directory)
-        if not vs:
-            raise FileNotFoundError(f"no checkpoint versions in {directory}")
-        version = vs[-1]
+        version = latest_complete_version(directory)
     params.reset()
     step = 0
     for p in version_files(directory, version):

@@ -94,7 +94,15 @@ k_lazy_insert(long long* __restrict__ idx_keys, int* __restrict__ idx_slot, unsi
                                                    (unsigned long long)key);
         if (old == kEmpty) {
           const int s = atomicAdd(count, 1);
-          if (s >= max_rows) { atomicExch(err, 1); slot = -1; break; }
+          if (s >= max_rows) {
+            // slab full: the key stays in the index but points at the spare row (slab row max_rows), the
+            // count is put back, the error flag is raised -- later probes of this key read a defined slot
+            atomicSub(count, 1);
+            idx_slot[h] = max_rows;
+            atomicExch(err, 1);
+            slot = max_rows;
+            break;
+          }
           idx_slot[h] = s;
           slot = (long long)s | (1ll << 62);   // bit 62: freshly claimed, needs initialisation
           break;
@@ -185,6 +193,7 @@ extern "C" int edl_lazy_clear(void* index, int64_t index_capacity, edl_stream_t 
   EDL_REQUIRE(index && pow2(index_capacity), EDL_EINVAL, "edl_lazy_clear: index null or capacity not a power of two");
   LazyIdx I = carve_idx(index, index_capacity);
   EDL_CUDA(cudaMemsetAsync(I.keys, 0xFF, (size_t)index_capacity * 8, (cudaStream_t)stream));
+  EDL_CUDA(cudaMemsetAsync(I.slots, 0, (size_t)index_capacity * 4, (cudaStream_t)stream));
   EDL_CUDA(cudaMemsetAsync(I.count, 0, 8, (cudaStream_t)stream));
   return EDL_OK;
 }

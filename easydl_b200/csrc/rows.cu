@@ -142,6 +142,54 @@ k_gather(const float4* __restrict__ src, int D4_rt, RowFn fn, int64_t n, const i
   }
 }
 
+// The same gather with the row index of the NEXT iteration fetched while the rows of this one are in
+// flight: the id / key / index load (and the table search behind a key) leaves the critical path, so a
+// thread's two row loads are outstanding nearly all the time instead of every other memory round trip.
+// For power-of-two row widths that divide the CTA the column of a thread is fixed (c = tid mod D4).
+template <int kD4, typename RowFn, bool kUseLayout>
+__global__ void __launch_bounds__(kThreads, 8)
+k_gather_pf(const float4* __restrict__ src, int D4_rt, RowFn fn, int64_t n, const int32_t* n_dev,
+            const int64_t* __restrict__ layout, float4* __restrict__ out) {
+  __shared__ EdlLayoutSmem L;
+  if (kUseLayout) {
+    edl_layout_load(&L, layout);
+    __syncthreads();
+  }
+  const int D4 = kD4 > 0 ? kD4 : D4_rt;
+  int64_t ne = n;
+  if (n_dev) { int64_t m = *n_dev; ne = m < n ? m : n; }
+  const int64_t total = ne * D4;
+  const int64_t stride = (int64_t)gridDim.x * kThreads;
+  int64_t e0 = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+  long long r[kUnroll], rn[kUnroll];
+#pragma unroll
+  for (int k = 0; k < kUnroll; ++k) {
+    const int64_t e = e0 + k * stride;
+    r[k] = e < total ? fn.row(&L, e / D4) : 0;
+  }
+  for (; e0 < total; e0 += stride * kUnroll) {
+    const int64_t en = e0 + stride * kUnroll;
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) {
+      const int64_t e = en + k * stride;
+      rn[k] = e < total ? fn.row(&L, e / D4) : 0;
+    }
+    float4 v[kUnroll];
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) {
+      const int64_t e = e0 + k * stride;
+      if (e < total) v[k] = src[r[k] * D4 + (int)(e % D4)];
+    }
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) {
+      const int64_t e = e0 + k * stride;
+      if (e < total) edl_st_cs(out + e, v[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) r[k] = rn[k];
+  }
+}
+
 // expand into a window of fields: item i = (sample b, field f of the window) lands at output row
 // b * F + f0 + f, so that several field groups of one [B, F] batch fill one [B * F, dim] array.
 template <int kD4>
@@ -223,11 +271,20 @@ int launch_gather(const float* src, int dim, RowFn fn, int64_t n, const int32_t*
   const int g = grid_for(n * D4, kUnroll);
   const float4* s4 = (const float4*)src;
   float4* o4 = (float4*)out;
-  switch (D4) {
-#define EDL_CASE(W) case W: k_gather<W, RowFn, kUseLayout><<<g, kThreads, 0, st>>>(s4, D4, fn, n, n_dev, layout, o4); break;
-    EDL_CASE(4) EDL_CASE(8) EDL_CASE(16) EDL_CASE(32) EDL_CASE(64)
+  if (edl_tune(EDL_TUNE_GATHER_IMPL) == 1) {
+    switch (D4) {
+#define EDL_CASE(W) case W: k_gather_pf<W, RowFn, kUseLayout><<<g, kThreads, 0, st>>>(s4, D4, fn, n, n_dev, layout, o4); break;
+      EDL_CASE(4) EDL_CASE(8) EDL_CASE(16) EDL_CASE(32) EDL_CASE(64)
 #undef EDL_CASE
-    default: k_gather<0, RowFn, kUseLayout><<<g, kThreads, 0, st>>>(s4, D4, fn, n, n_dev, layout, o4);
+      default: k_gather_pf<0, RowFn, kUseLayout><<<g, kThreads, 0, st>>>(s4, D4, fn, n, n_dev, layout, o4);
+    }
+  } else {
+    switch (D4) {
+#define EDL_CASE(W) case W: k_gather<W, RowFn, kUseLayout><<<g, kThreads, 0, st>>>(s4, D4, fn, n, n_dev, layout, o4); break;
+      EDL_CASE(4) EDL_CASE(8) EDL_CASE(16) EDL_CASE(32) EDL_CASE(64)
+#undef EDL_CASE
+      default: k_gather<0, RowFn, kUseLayout><<<g, kThreads, 0, st>>>(s4, D4, fn, n, n_dev, layout, o4);
+    }
   }
   EDL_LAUNCH_CHECK(who);
   return EDL_OK;

@@ -5,15 +5,14 @@
 #pragma once
 #include <mutex>
 #include "seg_common.cuh"
+#include "seg_stream.cuh"
 
 namespace {
 
-constexpr int kLongThrMin = 2;  // smallest allowed threshold (sizes the scratch)
-constexpr int kLongThrDefault = 16;  // segments longer than this go through the chunk path
+constexpr int kLongThrMin = 2;  // smallest allowed hot-id threshold (sizes the hot-id lists; knob long_thr, default 16)
 constexpr int kChunk = 64;     // gradient rows per chunk
 constexpr int kUnrollD = 4;    // independent row loads in flight per lane group (short path)
 constexpr int kUnrollC = 2;    // same, chunk path
-constexpr int kForkDefault = 1; // EDL_SEG_FORK default
 
 
 // kMode: 0 every segment; 1 only ids that occur once; 2 only ids that occur more than once
@@ -30,6 +29,7 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
   typedef Row<GT> R;
   edl_layout_load(&L, layout);
   __syncthreads();
+  epi.prepare();
   const int U = *n_unique;
   const int gl = threadIdx.x % kG;
   const unsigned ROWB_G = (unsigned)D4 * R::kBytes4;
@@ -68,7 +68,7 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
       base = atomicAdd(&counters[1], nch);
       li = atomicAdd(&counters[0], 1);
       long_list[li * 4 + 0] = u; long_list[li * 4 + 1] = base; long_list[li * 4 + 2] = nch;
-      long_list[li * 4 + 3] = 0;   // chunks completed so far
+      long_list[li * 4 + 3] = nch > 1 ? atomicAdd(&counters[3], nch) : 0;   // first partial row
     }
     // broadcast from the group's first lane; only this group's lanes take part
     const unsigned lane = threadIdx.x & 31u;
@@ -158,7 +158,8 @@ k_seg_classify(const int32_t* __restrict__ seg, const int32_t* __restrict__ n_un
   const int nch = (s1 - s0 + kChunk - 1) / kChunk;
   const int base = atomicAdd(&counters[1], nch);
   const int li = atomicAdd(&counters[0], 1);
-  ((int4*)long_list)[li] = make_int4(u, base, nch, 0);
+  const int pbase = nch > 1 ? atomicAdd(&counters[3], nch) : 0;   // partial rows only where they are combined
+  ((int4*)long_list)[li] = make_int4(u, base, nch, pbase);
   for (int c = 0; c < nch; ++c) {
     const int b = s0 + c * kChunk;
     ((int4*)chunk_list)[base + c] = make_int4(b, min(s1, b + kChunk), li, c);
@@ -199,13 +200,14 @@ template <int kG, int kC, typename GT, typename Epi>
 __global__ void __launch_bounds__(kThreads, (kC == 1 ? 8 : (kC == 2 ? 4 : 2)))
 k_seg_chunk(const unsigned char* __restrict__ grad, int D4, const int32_t* __restrict__ order,
             const int32_t* __restrict__ seg, const int32_t* __restrict__ counters,
-            const int32_t* __restrict__ chunk_list, int32_t* __restrict__ long_list,
+            const int32_t* __restrict__ chunk_list, const int32_t* __restrict__ long_list,
             double* __restrict__ partial, const int64_t* __restrict__ uniq,
             const int64_t* __restrict__ layout, Epi epi) {
   __shared__ EdlLayoutSmem L;
   typedef Row<GT> R;
   edl_layout_load(&L, layout);
   __syncthreads();
+  epi.prepare();
   const int n_chunks = counters[1];
   const int gl = threadIdx.x % kG;
   const unsigned lane = threadIdx.x & 31u;
@@ -216,7 +218,8 @@ k_seg_chunk(const unsigned char* __restrict__ grad, int D4, const int32_t* __res
   for (int ci = (int)(((int64_t)blockIdx.x * kThreads + threadIdx.x) / kG); ci < n_chunks; ci += groups) {
     const int4 ent = ((const int4*)chunk_list)[ci];
     const int b = ent.x, e = ent.y, li = ent.z;
-    const int u = long_list[li * 4], nch = long_list[li * 4 + 2];   // needed after the sum only
+    const int4 le = ((const int4*)long_list)[li];   // needed after the sum only
+    const int u = le.x, nch = le.z;
     double acc[kC][4];
 #pragma unroll
     for (int c = 0; c < kC; ++c) acc[c][0] = acc[c][1] = acc[c][2] = acc[c][3] = 0.0;
@@ -249,7 +252,7 @@ k_seg_chunk(const unsigned char* __restrict__ grad, int D4, const int32_t* __res
       for (int c = 0; c < kC; ++c) {
         const int col = gl + c * kG;
         if (col < D4) {
-          double2* dst = (double2*)(partial + (size_t)ci * D + col * 4);
+          double2* dst = (double2*)(partial + (size_t)(le.w + ent.w) * D + col * 4);
           dst[0] = make_double2(acc[c][0], acc[c][1]);
           dst[1] = make_double2(acc[c][2], acc[c][3]);
         }
@@ -281,12 +284,14 @@ k_seg_long_final(int D4, const int32_t* __restrict__ counters, const int32_t* __
   __shared__ EdlLayoutSmem L;
   edl_layout_load(&L, layout);
   __syncthreads();
+  epi.prepare();
   const int n_long = counters[0];
   const int gl = threadIdx.x % kG;
   const int groups = (int)((int64_t)gridDim.x * kThreads / kG);
   const int D = D4 * 4;
   for (int li = (int)(((int64_t)blockIdx.x * kThreads + threadIdx.x) / kG); li < n_long; li += groups) {
-    const int u = long_list[li * 4], base = long_list[li * 4 + 1], nch = long_list[li * 4 + 2];
+    const int4 le = ((const int4*)long_list)[li];
+    const int u = le.x, base = le.w, nch = le.z;   // base: first partial row
     if (nch <= 1) continue;   // finished inside k_seg_chunk
     const long long row = epi.row_of(&L, uniq, u);
     float4 p[kC], a0[kC], a1[kC];
@@ -338,41 +343,36 @@ k_seg_long_final(int D4, const int32_t* __restrict__ counters, const int32_t* __
   }
 }
 
+// One call = memset of the counters (update.cu), then
+//   main kernel   k_seg_stream (seg_impl 1, default) or k_seg_direct (0): ids with <= long_thr rows
+//   hot ids       k_seg_classify -> k_seg_chunk -> k_seg_long_final
+// seg_fork 1 (default): the hot-id branch runs on the device's helper stream beside the main kernel
+// (classify_side 1: from k_seg_classify on, so nothing precedes the main kernel on `st`).
 template <int kG, int kC, typename GT, typename Epi>
 int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t* seg,
                   const int32_t* seg_first, const int32_t* n_unique, int64_t max_unique, const int64_t* uniq,
                   const int64_t* layout, Epi epi, const DirectWs& W, cudaStream_t st) {
   const int64_t ctas = edl_cdiv(max_unique * kG, kThreads);
   EDL_REQUIRE(ctas < 0x7fffffff, EDL_ELIMIT, "segreduce: max_unique=%lld too large", (long long)max_unique);
-  static int long_thr = -1;
-  if (long_thr < 0) {
-    const char* e = getenv("EDL_LONG_THR");
-    long_thr = e ? std::max(kLongThrMin, atoi(e)) : kLongThrDefault;
-  }
-  // 8 CTAs x 256 threads per SM (<= 32 registers) and one row in flight per lane group: measured
-  // faster than fewer, fatter threads (profiles/r1_direct_variants.md) -- the loads that hide HBM
-  // latency come from occupancy, not from unrolling.
-  static int batch = -1;   // ids per lane group (EDL_DIRECT_BATCH=1 switches the index prefetch off)
-  if (batch < 0) { const char* e = getenv("EDL_DIRECT_BATCH"); batch = e ? atoi(e) : 2; }
-  // EDL_SEG_FORK=1: hot ids are listed first and their chunk kernels run on a helper stream beside
-  // k_seg_direct (their latency tail hides under it); 0: the three kernels in a row on `st`.
-  static int fork = -1;
-  if (fork < 0) { const char* e = getenv("EDL_SEG_FORK"); fork = e ? atoi(e) : kForkDefault; }
+  const int long_thr = std::max(kLongThrMin, edl_tune(EDL_TUNE_LONG_THR));
+  const int batch = edl_tune(EDL_TUNE_DIRECT_BATCH);
+  const int fork = edl_tune(EDL_TUNE_SEG_FORK);
+  const int impl = edl_tune(EDL_TUNE_SEG_IMPL);
+  const bool cls_side = fork && edl_tune(EDL_TUNE_CLASSIFY_SIDE);
+  const bool classify = fork || impl == 1;   // k_seg_direct can list the hot ids itself (unforked launch)
   std::unique_lock<std::mutex> lock(fork_mutex(), std::defer_lock);
   ForkRes* F = nullptr;
   cudaStream_t st_hot = st;
-  int32_t* reg_counters = W.counters;
   if (fork) {
     lock.lock();
     int rc = fork_res(&F);
     if (rc) return rc;
-    k_seg_classify<<<(unsigned)edl_cdiv(max_unique, kThreads), kThreads, 0, st>>>(seg, n_unique, W.counters, W.long_list,
-                                                                                 W.chunk_list, long_thr);
-    EDL_CUDA(cudaEventRecord(F->fork, st));
-    EDL_CUDA(cudaStreamWaitEvent(F->side, F->fork, 0));
     st_hot = F->side;
-    reg_counters = nullptr;
   }
+  auto launch_classify = [&](cudaStream_t s) {
+    k_seg_classify<<<(unsigned)edl_cdiv(max_unique, kThreads), kThreads, 0, s>>>(seg, n_unique, W.counters, W.long_list,
+                                                                                W.chunk_list, long_thr);
+  };
   auto launch_hot = [&]() {
     const int64_t gc = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_chunks * kG, kThreads), EDL_SM_COUNT * 8));
     k_seg_chunk<kG, kC, GT, Epi><<<(unsigned)gc, kThreads, 0, st_hot>>>((const unsigned char*)grad, D4, order, seg,
@@ -382,24 +382,39 @@ int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t*
     k_seg_long_final<kG, kC, Epi><<<(unsigned)gf, kThreads, 0, st_hot>>>(D4, W.counters, W.long_list, W.partial, uniq,
                                                                          layout, epi);
   };
-  if (fork) launch_hot();
-#define EDL_DARGS (const unsigned char*)grad, D4, order, seg, seg_first, n_unique, uniq, layout, epi, reg_counters, W.long_list, W.chunk_list, long_thr
-  if constexpr (kC == 1) {
-    if (batch == 2)
-      k_seg_direct<kG, kC, GT, Epi, 8, 1, 0, kThreads, 2><<<(unsigned)edl_cdiv(ctas, 2), kThreads, 0, st>>>(EDL_DARGS);
-    else
-      k_seg_direct<kG, kC, GT, Epi, 8, 1><<<(unsigned)ctas, kThreads, 0, st>>>(EDL_DARGS);
-  } else {
-    k_seg_direct<kG, kC, GT, Epi, (kC == 2 ? 4 : 2), 1><<<(unsigned)ctas, kThreads, 0, st>>>(EDL_DARGS);
+  if (fork) {
+    if (!cls_side) launch_classify(st);
+    EDL_CUDA(cudaEventRecord(F->fork, st));
+    EDL_CUDA(cudaStreamWaitEvent(F->side, F->fork, 0));
+    if (cls_side) launch_classify(F->side);
+    launch_hot();
+  } else if (classify) {
+    launch_classify(st);
   }
+  if (impl == 1) {
+    int rc = launch_stream_main<kG, kC, GT, Epi>(grad, D4, order, seg, seg_first, n_unique, max_unique, uniq, layout,
+                                                 epi, W.counters + 2, long_thr, st);
+    if (rc) return rc;
+  } else {
+    int32_t* reg_counters = classify ? nullptr : W.counters;
+#define EDL_DARGS (const unsigned char*)grad, D4, order, seg, seg_first, n_unique, uniq, layout, epi, reg_counters, W.long_list, W.chunk_list, long_thr
+    if constexpr (kC == 1) {
+      if (batch == 2)
+        k_seg_direct<kG, kC, GT, Epi, 8, 1, 0, kThreads, 2><<<(unsigned)edl_cdiv(ctas, 2), kThreads, 0, st>>>(EDL_DARGS);
+      else
+        k_seg_direct<kG, kC, GT, Epi, 8, 1><<<(unsigned)ctas, kThreads, 0, st>>>(EDL_DARGS);
+    } else {
+      k_seg_direct<kG, kC, GT, Epi, (kC == 2 ? 4 : 2), 1><<<(unsigned)ctas, kThreads, 0, st>>>(EDL_DARGS);
+    }
 #undef EDL_DARGS
+  }
   if (fork) {
     EDL_CUDA(cudaEventRecord(F->join, F->side));
     EDL_CUDA(cudaStreamWaitEvent(st, F->join, 0));
   } else {
     launch_hot();
   }
-  EDL_LAUNCH_CHECK("k_seg_direct / k_seg_chunk");
+  EDL_LAUNCH_CHECK("segmented reduce kernels");
   return EDL_OK;
 }
 

@@ -6,52 +6,38 @@
 // row with every fp32 operation rounded separately (explicit __f*_rn, so nvcc cannot contract
 // to FMA and the result matches the NumPy oracle op for op).
 //
-//   seg_direct.cuh  register path: one lane group per id, hot ids cut into chunks (default)
-//   seg_tile.cu     shared-memory staged path: persistent CTAs over the sorted positions,
-//                   asynchronous row copies into a 3-stage ring (EDL_SEG_IMPL=tile)
+//   seg_stream.cuh  main kernel (default): persistent warps, rows streamed through a private
+//                   shared-memory ring with cp.async
+//   seg_direct.cuh  the register-path main kernel (knob seg_impl = 0), the hot-id kernels and the launch
 #include "seg_common.cuh"
 #include "seg_direct.cuh"
 
-int edl_seg_run_tile(const SegCall& c, const SegWs& W);   // seg_tile.cu
-
 namespace {
 
-struct Ws { SegWs tile; DirectWs direct; size_t zero_bytes; size_t bytes; };
+struct Ws { DirectWs direct; size_t zero_bytes; size_t bytes; };
 
-// [flags | ticket | direct counters] cleared per call, then tile carries, then direct lists
+// [counters] cleared per call, then the hot-id lists, then the float64 partial rows.  Partial rows exist
+// only for ids that span more than one chunk (more than kChunk gradient rows): at most
+// n / kChunk + n / (kChunk + 1) chunks belong to such ids.
 Ws carve_ws(void* ws, int64_t n_rows, int dim) {
   Ws w; char* p = (char*)ws;
   size_t off = 0;
-  w.tile.flags = (int32_t*)(p + off); off += (size_t)kMaxGrid * 4 * sizeof(int32_t);
-  w.tile.ticket = (unsigned*)(p + off); off += 256;
   w.direct.counters = (int32_t*)(p + off); off += 256;
   w.zero_bytes = off;
-  w.tile.zero_bytes = off;
-  w.tile.carry_h = (double*)(p + off); off += (size_t)kMaxGrid * dim * sizeof(double);
-  w.tile.carry_t = (double*)(p + off); off += (size_t)kMaxGrid * dim * sizeof(double);
   const int64_t n = n_rows > 0 ? n_rows : 0;
   w.direct.max_long = n / (kLongThrMin + 1) + 1;
   w.direct.max_chunks = n / kChunk + w.direct.max_long + 1;
+  const int64_t max_partial = n / kChunk + n / (kChunk + 1) + 2;
   w.direct.long_list = (int32_t*)(p + off); off = edl_align_up(off + (size_t)w.direct.max_long * 4 * 4, 256);
   w.direct.chunk_list = (int32_t*)(p + off); off = edl_align_up(off + (size_t)w.direct.max_chunks * 4 * 4, 256);
-  w.direct.partial = (double*)(p + off); off = edl_align_up(off + (size_t)w.direct.max_chunks * dim * 8, 256);
-  w.tile.bytes = off;
+  w.direct.partial = (double*)(p + off); off = edl_align_up(off + (size_t)max_partial * dim * 8, 256);
   w.bytes = off;
   return w;
 }
 
-bool use_tile_impl() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("EDL_SEG_IMPL");
-    v = (e && e[0] == 't') ? 1 : 0;
-  }
-  return v == 1;
-}
-
 int run_call(const SegCall& c, const Ws& W) {
-  EDL_CUDA(cudaMemsetAsync(W.tile.flags, 0, W.zero_bytes, c.st));
-  return use_tile_impl() ? edl_seg_run_tile(c, W.tile) : seg_run_direct(c, W.direct);
+  EDL_CUDA(cudaMemsetAsync(W.direct.counters, 0, W.zero_bytes, c.st));
+  return seg_run_direct(c, W.direct);
 }
 
 int check_common(const char* who, const void* grad, int dim, const int32_t* order,
@@ -115,6 +101,7 @@ extern "C" int edl_segreduce_update(float* slab, float* slot0, float* slot1, int
   EDL_REQUIRE((((uintptr_t)slab | (uintptr_t)slot0 | (uintptr_t)slot1) & 15) == 0, EDL_EINVAL,
               "edl_segreduce_update: rows must be 16-byte aligned");
   OptDev o;
+  o.lr_dev = opt->lr_dev;
   o.lr = opt->lr; o.eps = opt->eps; o.b1 = opt->beta1; o.b2 = opt->beta2;
   o.omb1 = 1.0f - opt->beta1;  // fp32 subtraction, as the oracle does
   o.omb2 = 1.0f - opt->beta2;

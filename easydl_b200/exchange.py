@@ -218,6 +218,15 @@ class PeerExchange:
             self.dist.all_gather_into_tensor(allc, t, group=self.group)
             allc = allc.cpu()                                   # [src, dst, k]: the step's one host sync
             self.M = allc[:, :, 0].clone()
+            # Every rank holds the whole matrix here, so every rank sees the same overflow and raises
+            # before ANY copy of the step is issued: no rank writes past another rank's region while
+            # that rank has already given up.  (Both directions: rows received forward = column sums,
+            # rows received on the way back = row sums.)
+            worst = int(max(self.M.sum(0).max(), self.M.sum(1).max())) if self.M.numel() else 0
+            if worst > self.cap:
+                raise RuntimeError(f"PeerExchange: a rank would receive {worst} rows in one round, the "
+                                   f"receive buffers hold {self.cap}; raise capacity_rows")
+            self.late_check()
             self.gen ^= 1
             return allc[:, self.rank].contiguous()
         if kind != "a2av":
@@ -249,6 +258,13 @@ class PeerExchange:
             soff += n
         self._fence()
         return self._recv_view(tag, n_recv)
+
+    def late_check(self):
+        """Raise if a fence of an EARLIER step timed out (the kernel leaves a mark in own_flags[world]);
+        read at the counts round, where the host is synchronised with the device anyway."""
+        if int(self.own_flags[self.world].item()) != 0:
+            raise RuntimeError("PeerExchange: a peer did not reach an exchange fence in time; the data of that "
+                               "round is incomplete")
 
     def _recv_view(self, tag, n_recv):
         rb, roff = self.row_bytes[tag], self.region_off[(self.gen, tag)]

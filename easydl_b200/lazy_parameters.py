@@ -51,6 +51,9 @@ class LazyShardParameters:
         off = self.index_capacity * 12
         self.status = self.index[off:off + 8].view(torch.int32)     # [rows materialised, overflow]
         self.touched = None                                          # every stored row is a touched row
+        self.lr_dev = torch.zeros(1, dtype=torch.float32, device=self.device)   # see ShardParameters.stage_rate
+        self._lr_ring = None
+        self._slot_buf = None
 
     num_shards = property(lambda self: self.layout.num_shards)
     shard = property(lambda self: self.layout.shard)
@@ -79,10 +82,15 @@ class LazyShardParameters:
         return out
 
     # ------------------------------------------------------------------ A4 + A5
-    def _slots_for(self, keys: torch.Tensor, n_dev=None) -> torch.Tensor:
+    def _slots_for(self, keys: torch.Tensor, n_dev=None, reuse: bool = False) -> torch.Tensor:
         lib = _lib.load()
         n = keys.numel()
-        slots = torch.empty(max(n, 1), dtype=torch.int64, device=self.device)
+        if reuse:   # the step's own scratch: one buffer, grown on demand, so a captured step allocates nothing
+            if self._slot_buf is None or self._slot_buf.numel() < max(n, 1):
+                self._slot_buf = torch.empty(max(n, 1), dtype=torch.int64, device=self.device)
+            slots = self._slot_buf
+        else:
+            slots = torch.empty(max(n, 1), dtype=torch.int64, device=self.device)
         s1 = self.slots[1] if len(self.slots) > 1 else None
         check(lib.edl_lazy_insert(self.index.data_ptr(), self.index_capacity, self.slab.data_ptr(),
                                   self.slots[0].data_ptr(), K._ptr(s1), self.dim, self.max_rows, K._ptr(keys), n,
@@ -91,14 +99,29 @@ class LazyShardParameters:
                                   slots.data_ptr(), K._stream()), "edl_lazy_insert")
         return slots
 
+    _RING = 1024
+
+    def stage_rate(self, step: int):
+        """rate(step) -> lr_dev on the current stream (same contract as ShardParameters.stage_rate)."""
+        if self._lr_ring is None:
+            self._lr_ring = torch.zeros(self._RING, dtype=torch.float32).pin_memory()
+        k = step % self._RING
+        self._lr_ring[k] = self.opt.rate(step)
+        self.lr_dev.copy_(self._lr_ring[k:k + 1], non_blocking=True)
+
     def apply_gradients(self, uq: K.UniqueResult, grad: torch.Tensor, max_unique: Optional[int] = None,
-                        workspace=None):
-        self.step += 1
-        slots = self._slots_for(uq.uniq, uq.n_unique)
+                        workspace=None, n_rows: Optional[int] = None, bump_step: bool = True,
+                        rate_on_device: bool = False):
+        """Same signature as ShardParameters.apply_gradients: insert-if-absent for the unique keys, then the
+        fused reduce + optimizer on their slab rows."""
+        if bump_step:
+            self.step += 1
+        slots = self._slots_for(uq.uniq, uq.n_unique, reuse=True)
         s1 = self.slots[1] if len(self.slots) > 1 else None
+        opt = self.opt.params(self.step, self.lr_dev.data_ptr() if rate_on_device else 0)
         K.segreduce_update(self.slab, self.slots[0], s1, slots, uq.order, uq.seg_offsets, uq.n_unique,
                            uq.n if max_unique is None else max_unique, grad, None,
-                           self.opt.params(self.step), None, workspace, seg_first=uq.seg_first)
+                           opt, None, workspace, seg_first=uq.seg_first, n_rows=n_rows)
 
     # ------------------------------------------------------------------ A6
     def export_records(self) -> ShardRecords:

@@ -38,12 +38,17 @@ class OptimizerSpec:
     def slot_init(self, k: int) -> float:
         return self.init_accum if self.kind == EDL_OPT_ADAGRAD else 0.0
 
-    def params(self, step: int) -> OptParams:
-        """Kernel parameters for global step `step` (1-based).  Adam's bias-corrected rate
-        lr_t = lr*sqrt(1-b2^t)/(1-b1^t) is evaluated in float64 here and passed as fp32."""
+    def rate(self, step: int) -> float:
+        """The fp32 rate of global step `step` (1-based).  Adam's bias-corrected rate
+        lr_t = lr*sqrt(1-b2^t)/(1-b1^t) is evaluated in float64 and rounded once."""
         if self.kind == EDL_OPT_ADAGRAD:
             lr = self.lr
         else:
             lr = self.lr * math.sqrt(1.0 - self.beta2 ** step) / (1.0 - self.beta1 ** step)
-        return OptParams(self.kind, float(np.float32(lr)), float(np.float32(self.eps)),
-                         float(np.float32(self.beta1)), float(np.float32(self.beta2)))
+        return float(np.float32(lr))
+
+    def params(self, step: int, lr_dev: int = 0) -> OptParams:
+        """Kernel parameters for global step `step`.  lr_dev: address of a device float the kernels
+        read the rate from instead (the caller stores rate(step) there; CUDA-graph replay)."""
+        return OptParams(self.kind, self.rate(step), float(np.float32(self.eps)),
+                         float(np.float32(self.beta1)), float(np.float32(self.beta2)), lr_dev or None)

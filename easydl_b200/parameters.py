@@ -56,6 +56,10 @@ class ShardParameters:
         self.slots = [torch.empty((n, dim), dtype=torch.float32, device=self.device)
                       for _ in range(opt.n_slots)]
         self.touched = torch.zeros((n + 31) // 32 + 1, dtype=torch.int32, device=self.device)
+        # the optimizer rate as a device scalar, for launch sequences that are captured once and
+        # replayed (Adam's lr_t changes every step): stage_rate() copies rate(step) into it
+        self.lr_dev = torch.zeros(1, dtype=torch.float32, device=self.device)
+        self._lr_ring = None
         if init:
             self.reset()
 
@@ -87,16 +91,30 @@ class ShardParameters:
         return K.gather_keys(self.slab, keys, self._layout_arg, n_dev=n_dev, out=out)
 
     # ------------------------------------------------------------------ A4 + A5
+    _RING = 1024
+
+    def stage_rate(self, step: int):
+        """Enqueue rate(step) -> lr_dev on the current stream (from a ring of pinned host slots, so the
+        host never waits).  Call before replaying a launch sequence captured with rate_on_device."""
+        if self._lr_ring is None:
+            self._lr_ring = torch.zeros(self._RING, dtype=torch.float32).pin_memory()
+        k = step % self._RING
+        self._lr_ring[k] = self.opt.rate(step)
+        self.lr_dev.copy_(self._lr_ring[k:k + 1], non_blocking=True)
+
     def apply_gradients(self, uq: K.UniqueResult, grad: torch.Tensor, max_unique: Optional[int] = None,
-                        workspace=None, n_rows: Optional[int] = None, bump_step: bool = True):
+                        workspace=None, n_rows: Optional[int] = None, bump_step: bool = True,
+                        rate_on_device: bool = False):
         """Segment-sum grad rows per unique key and run the optimizer on the touched rows.
-        bump_step=False: a further part of the same training step (disjoint ids), same step number."""
+        bump_step=False: a further part of the same training step (disjoint ids), same step number.
+        rate_on_device: the kernels read the rate from lr_dev (see stage_rate) instead of taking it by value."""
         if bump_step:
             self.step += 1
         slot1 = self.slots[1] if len(self.slots) > 1 else None
+        opt = self.opt.params(self.step, self.lr_dev.data_ptr() if rate_on_device else 0)
         K.segreduce_update(self.slab, self.slots[0], slot1, uq.uniq, uq.order, uq.seg_offsets,
                            uq.n_unique, uq.n if max_unique is None else max_unique, grad,
-                           self._layout_arg, self.opt.params(self.step), self.touched, workspace,
+                           self._layout_arg, opt, self.touched, workspace,
                            seg_first=uq.seg_first, n_rows=n_rows)
 
     # ------------------------------------------------------------------ A6

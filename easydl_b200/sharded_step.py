@@ -47,7 +47,7 @@ class CudaOps:
 
     def lookup_into(self, keys, out):
         """Gather into `out`, which may be peer-mapped memory of another GPU."""
-        K.gather_keys(self.params.slab, keys.contiguous(), self.params._layout_arg, out=out)
+        self.params.lookup(keys.contiguous(), out=out)     # dense or lazily materialised shard alike
 
     def expand(self, rows_in, uq, part):
         return K.expand(rows_in, K.compose_index(uq.inverse, part.pos))

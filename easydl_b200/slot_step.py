@@ -238,8 +238,7 @@ class SlotShardedStep:
     def _gather_for(self, s: int):
         b, g = self.buf, self.gen
         k = b.own_region(g, "keys")[s * b.stride:s * b.stride + self.limit]
-        K.gather_keys(self.params.slab, k, self.params._layout_arg, n_dev=b.own_region(g, "counts")[s:s + 1],
-                      out=b.remote_rows_slot(s, g, self.limit))
+        self.params.lookup(k, n_dev=b.own_region(g, "counts")[s:s + 1], out=b.remote_rows_slot(s, g, self.limit))
 
     def phase_b(self, overlap: bool = False):
         if not overlap:

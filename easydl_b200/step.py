@@ -43,10 +43,10 @@ class SparseStep:
         self.ws_unique = torch.empty(lib.edl_unique_workspace_bytes(N, self.key_bits, self.F, self.field_bits),
                                      dtype=torch.uint8, device=dev)
         self.ws_seg = torch.empty(lib.edl_segreduce_workspace_bytes(N, N, D), dtype=torch.uint8, device=dev)
-        # launches per step (for bench.py's gpu_launches): gather 1; unique 3/pass + 3; update 3 (+ k_seg_classify when forked) + memset
+        # launches per step (for bench.py's gpu_launches): gather 1; unique 3/pass + 3; update 4
+        # (k_seg_classify, main kernel, k_seg_chunk, k_seg_long_final) + one memset node
         passes = min((self.key_bits + 7) // 8, (self.field_bits + 7) // 8)
-        fork = int(os.environ.get("EDL_SEG_FORK", "1")) != 0   # forked update adds k_seg_classify
-        self.launches_per_step = 1 + 3 * passes + 3 + 3 + int(fork)  # + one memset node
+        self.launches_per_step = 1 + 3 * passes + 3 + 4
         self.last_n_unique = self.uq.n_unique
         # The lookup does not need the dedup (it gathers by id), so the two can run side by side:
         # the radix passes are short latency-bound kernels, the gather is one long HBM-bound one.
@@ -62,16 +62,17 @@ class SparseStep:
         return K.unique(ids.view(-1), self.field_base, self.key_bits, field_bits=self.field_bits,
                         want_inverse=False, want_counts=False, out=self.uq, workspace=self.ws_unique)
 
-    def update(self, ids: torch.Tensor, grad: torch.Tensor, uq: Optional[K.UniqueResult] = None):
+    def update(self, ids: torch.Tensor, grad: torch.Tensor, uq: Optional[K.UniqueResult] = None,
+               rate_on_device: bool = False):
         """grad f32 [B*F, dim]: upstream gradient of emb."""
         if uq is None:
             uq = self.dedup(ids)
-        self.params.apply_gradients(uq, grad, self.N, self.ws_seg)
+        self.params.apply_gradients(uq, grad, self.N, self.ws_seg, rate_on_device=rate_on_device)
 
-    def run(self, ids: torch.Tensor, grad: torch.Tensor) -> torch.Tensor:
+    def run(self, ids: torch.Tensor, grad: torch.Tensor, rate_on_device: bool = False) -> torch.Tensor:
         if self.side is None:
             emb = self.lookup(ids)
-            self.update(ids, grad)
+            self.update(ids, grad, rate_on_device=rate_on_device)
             return emb
         cur = torch.cuda.current_stream()
         self.side.wait_stream(cur)
@@ -79,7 +80,7 @@ class SparseStep:
             uq = self.dedup(ids)
         emb = self.lookup(ids)
         cur.wait_stream(self.side)
-        self.update(ids, grad, uq)
+        self.update(ids, grad, uq, rate_on_device=rate_on_device)
         return emb
 
 
@@ -87,13 +88,11 @@ class GraphedStep:
     """A SparseStep captured into CUDA graphs for one fixed (ids, grad) buffer pair: the 17
     launches of a step cost one graph launch instead of 17 trips through the driver.  Three
     graphs (lookup / dedup / update) so that a caller can time the phases with events between
-    them, plus one graph of the whole step.  Adagrad only: Adam's bias-corrected rate changes
-    every step and is a by-value kernel argument."""
+    them, plus one graph of the whole step.  The optimizer rate is read from a device scalar
+    (ShardParameters.lr_dev) that run() refreshes before every replay, so Adam's bias-corrected
+    rate, which changes every step, replays correctly."""
 
     def __init__(self, step: SparseStep, ids: torch.Tensor, grad: torch.Tensor):
-        from ._lib import EDL_OPT_ADAGRAD
-        if step.params.opt.kind != EDL_OPT_ADAGRAD:
-            raise ValueError("GraphedStep supports Adagrad only")
         self.step, self.ids, self.grad = step, ids, grad
         cur = torch.cuda.current_stream()
         side = torch.cuda.Stream()
@@ -109,12 +108,14 @@ class GraphedStep:
         with torch.cuda.graph(self.g_dedup):
             step.dedup(ids)
         with torch.cuda.graph(self.g_update):
-            step.update(ids, grad, step.uq)
+            step.update(ids, grad, step.uq, rate_on_device=True)
         with torch.cuda.graph(self.g_all):
-            step.run(ids, grad)
+            step.run(ids, grad, rate_on_device=True)
         step.params.step = host_step
 
     def run(self):
+        p = self.step.params
+        p.stage_rate(p.step + 1)
         self.g_all.replay()
-        self.step.params.step += 1
+        p.step += 1
         return self.step.emb

@@ -53,11 +53,25 @@ typedef void* edl_stream_t; /* cudaStream_t */
 int edl_version(void);
 const char* edl_last_error_string(void);
 
+/* ---- launch-shape knobs (no lineage counterpart: operational switches of this library) ----
+ * Integer knobs that choose between kernel shapes with identical results.  Each starts at its
+ * default, or at the value of its environment variable if that is set when the library first reads
+ * a knob, and can be changed at any time (a launch already issued keeps what it read).
+ *   long_thr      (EDL_LONG_THR, 16)      ids with more gradient rows go through the hot-id chunk kernels
+ *   seg_fork      (EDL_SEG_FORK, 1)       hot-id kernels on the helper stream beside the main reduce kernel
+ *   classify_side (EDL_CLASSIFY_SIDE, 1)  forked launch: the hot-id listing runs on the helper stream too
+ *   seg_impl      (EDL_SEG_IMPL, 1)       main reduce kernel: 1 = k_seg_stream (cp.async ring), 0 = k_seg_direct
+ *   stream_ctas   (EDL_STREAM_CTAS, 3)    k_seg_stream: persistent CTAs per SM (capped by shared memory)
+ *   direct_batch  (EDL_DIRECT_BATCH, 2)   k_seg_direct: ids per lane group
+ *   gather_impl   (EDL_GATHER_IMPL, 1)    gather kernels: 1 = next iteration's row index prefetched
+ * Unknown names and out-of-range values return EDL_EINVAL. */
+int edl_tuning_set(const char* name, int value);
+int edl_tuning_get(const char* name, int* value_out);
+
 /* ---- row initialisation (SPEC "Row initialisation"; lineage EmbeddingTable lazy init) ---
  * Fills slab rows [row_begin, row_begin + n_rows) of this shard's slab with the pure
- * function init(seed, t, id, c).  layout may be NULL (S == 1: slab row == fused key, tables
- * located through key_base passed as `layout`-less call is not possible, so layout is
- * required here). */
+ * function init(seed, t, id, c).  layout is REQUIRED here, also for S == 1: the table of a slab
+ * row, and with it the id the initialiser hashes, is found through local_base. */
 int edl_init_rows(float* slab, int dim, const int64_t* layout, int64_t row_begin, int64_t n_rows,
                   uint64_t seed, edl_stream_t stream);
 /* value fill for optimizer slots (Adagrad init_accum, Adam zeros) */
@@ -115,7 +129,7 @@ int edl_unique_static(const int64_t* ids, int64_t n, const int32_t* n_dev, const
                       edl_stream_t stream);
 
 /* ---- A2 hash-mod partition (lineage int_to_id / scatter_embedding_vector) --------------
- * Stable partition of keys[0..n) by (per-table id mod S'), S' = num_shards (1..256), tables
+ * Stable partition of keys[0..n) by (per-table id mod S'), S' = num_shards (1..255), tables
  * located through `layout` (only T and key_base are read; NULL = single table, id == key).
  * Outputs: keys_out[n] grouped by shard, offsets[S'+1] int32, perm[n] int32 (original
  * position of each output), pos[n] int32 (nullable; inverse of perm). */
@@ -165,7 +179,9 @@ int edl_compose_index(const int32_t* index, const int32_t* map, int64_t n, int32
  * be captured into a CUDA graph through it.  The helper stream and its two events are created on
  * the first call on a device, which therefore must happen outside any stream capture.  Calls from
  * several host threads on one device are serialised over the launch sequence by a mutex.
- * EDL_SEG_FORK=0 in the environment keeps every launch on `stream` (no helper stream is made). */
+ * Knob seg_fork = 0 (EDL_SEG_FORK=0 in the environment) keeps every launch on `stream` (no helper
+ * stream is made).  The main kernel takes its shared-memory opt-in (cudaFuncSetAttribute) on the first
+ * call of each shape on a device: one more reason for the first call to come before any capture. */
 size_t edl_segreduce_workspace_bytes(int64_t max_unique, int64_t n_rows, int dim);
 int edl_segreduce(const float* grad, int dim, const int32_t* order, const int32_t* seg_offsets,
                   const int32_t* seg_first /* nullable */, const int32_t* n_unique_dev, int64_t max_unique, int64_t n_rows,
@@ -178,7 +194,7 @@ int edl_segreduce(const float* grad, int dim, const int32_t* order, const int32_
  * grad_f64 != 0), rounded once to fp32; row = row(uniq[u]) through layout;
  * Adagrad: acc += g*g; p -= lr*g/(sqrt(acc)+eps)                       (slot0 = acc)
  * Adam   : m = b1*m+(1-b1)*g; v = b2*v+((1-b2)*g)*g; p -= lr_t*m/(sqrt(v)+eps)
- *          (slot0 = m, slot1 = v; lr_t computed by the caller in float64)
+ *          (slot0 = m, slot1 = v; lr_t computed by the caller in float64, passed in `lr` or through `lr_dev`)
  * every operation rounded to fp32 separately (no FMA contraction).
  * touched (nullable): bitmap, one bit per slab row, set for every updated row (A6 export). */
 typedef struct edl_opt_params {
@@ -187,6 +203,9 @@ typedef struct edl_opt_params {
   float eps;
   float beta1;  /* Adam only */
   float beta2;  /* Adam only */
+  const float* lr_dev; /* nullable DEVICE pointer: when set, the kernels read the rate from it instead of
+                        * `lr` -- a captured CUDA graph then sees the value the caller stored there before
+                        * each replay (Adam's lr_t changes every step).  Zero the struct before filling it. */
 } edl_opt_params;
 
 int edl_segreduce_update(float* slab, float* slot0, float* slot1, int dim, const int64_t* uniq,

@@ -359,40 +359,67 @@ def test_errors_are_reported_not_thrown(cuda):
         K.unique(torch.zeros(4, dtype=torch.int64), None, 8)
 
 
-def test_update_launch_variants_agree(cuda):
-    """The update's two launch shapes (hot-id kernels on the forked helper stream, the default, and
-    all launches in a row, EDL_SEG_FORK=0) and the step with / without the dedup beside the lookup
-    give the same bits.  The switches are read once per process, so the other shapes run in a child."""
-    import subprocess, sys, os, hashlib
-    prog = r'''
-import hashlib, numpy as np, torch
-from easydl_b200.criteo import CriteoSynthetic
-from easydl_b200.optimizer import OptimizerSpec
-from easydl_b200.parameters import ShardParameters
-from easydl_b200.step import SparseStep
-dev = torch.device("cuda:0")
-rows = [50_000] * 26
-P = ShardParameters(rows, 64, OptimizerSpec.adagrad(), device=dev)
-src = CriteoSynthetic(rows, 8192, alpha=1.2)
-st = SparseStep(P, 8192)
-h = hashlib.sha256()
-for k in range(3):
-    ids = torch.from_numpy(src.ids(k)).to(dev)
-    grad = torch.from_numpy(src.grad(64, k)).to(dev)
-    emb = st.run(ids, grad)
-    torch.cuda.synchronize()
-    h.update(emb.cpu().numpy().tobytes())
-h.update(P.slab.cpu().numpy().tobytes()); h.update(P.slots[0].cpu().numpy().tobytes())
-print("DIGEST", h.hexdigest())
-'''
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+def _three_steps_digest(dev, opt, dim=64, alpha=1.2):
+    import hashlib
+    from easydl_b200.criteo import CriteoSynthetic
+    from easydl_b200.parameters import ShardParameters
+    from easydl_b200.step import SparseStep
+    rows = [50_000] * 26
+    P = ShardParameters(rows, dim, opt, device=dev)
+    src = CriteoSynthetic(rows, 8192, alpha=alpha)
+    st = SparseStep(P, 8192)
+    h = hashlib.sha256()
+    for k in range(3):
+        ids = torch.from_numpy(src.ids(k)).to(dev)
+        grad = torch.from_numpy(src.grad(dim, k)).to(dev)
+        emb = st.run(ids, grad)
+        torch.cuda.synchronize()
+        h.update(emb.cpu().numpy().tobytes())
+    h.update(P.slab.cpu().numpy().tobytes())
+    for s in P.slots:
+        h.update(s.cpu().numpy().tobytes())
+    return h.hexdigest()
+
+
+@pytest.mark.parametrize("opt_name,dim", [("adagrad", 64), ("adam", 64), ("adagrad", 16), ("adam", 128), ("adagrad", 256)])
+def test_update_launch_variants_agree(cuda, opt_name, dim):
+    """Every launch shape of the update gives the same bits: the streamed main kernel (default) and
+    the register-path one, hot-id kernels on the helper stream or in a row, the hot-id listing on
+    either stream, different hot-id thresholds and ring occupancies, the prefetching gather and the
+    plain one.  The knobs are switched in-process (edl_tuning_set)."""
+    from easydl_b200 import _lib
+    from easydl_b200.optimizer import OptimizerSpec
+    knobs = ("seg_impl", "seg_fork", "classify_side", "long_thr", "stream_ctas", "direct_batch", "gather_impl")
+    saved = {k: _lib.tuning_get(k) for k in knobs}
+    variants = [
+        dict(),                                               # defaults
+        dict(seg_impl=0, gather_impl=0),                      # round-1 kernels
+        dict(seg_impl=0, seg_fork=0, direct_batch=1),
+        dict(seg_impl=1, seg_fork=0),
+        dict(seg_impl=1, classify_side=0, long_thr=4, stream_ctas=1),
+        dict(seg_impl=1, long_thr=100, stream_ctas=2),
+        dict(seg_impl=0, long_thr=3),
+    ]
+    opt = OptimizerSpec.adagrad() if opt_name == "adagrad" else OptimizerSpec.adam()
     digests = []
-    for fork, overlap in (("1", "1"), ("0", "0"), ("1", "0"), ("0", "1")):
-        env = dict(os.environ, EDL_SEG_FORK=fork, EDL_STEP_OVERLAP=overlap, PYTHONPATH=root)
-        out = subprocess.run([sys.executable, "-c", prog], env=env, cwd=root, capture_output=True, text=True, timeout=600)
-        assert out.returncode == 0, out.stderr[-2000:]
-        digests.append([l for l in out.stdout.splitlines() if l.startswith("DIGEST")][0])
+    try:
+        for v in variants:
+            for k in knobs:
+                _lib.tuning_set(k, v.get(k, saved[k]))
+            digests.append(_three_steps_digest(cuda, opt, dim))
+    finally:
+        for k in knobs:
+            _lib.tuning_set(k, saved[k])
     assert len(set(digests)) == 1, digests
+
+
+def test_tuning_knobs_reject_bad_input(cuda):
+    from easydl_b200 import _lib
+    with pytest.raises(_lib.EdlError, match="unknown knob"):
+        _lib.tuning_set("no_such_knob", 1)
+    with pytest.raises(_lib.EdlError, match="outside"):
+        _lib.tuning_set("seg_impl", 7)
+    assert _lib.tuning_get("long_thr") >= 2
 
 
 def test_c_host_program(cuda, tmp_path):

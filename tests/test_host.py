@@ -195,3 +195,39 @@ def test_header_is_plain_c_and_c_host_links(tmp_path):
     r = subprocess.run(cmd, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     assert os.path.exists(tmp_path / "c_host")
+
+
+def _touch_version(d, v, shards, S):
+    import os
+    os.makedirs(os.path.join(d, f"version-{v}"), exist_ok=True)
+    for s in shards:
+        open(os.path.join(d, f"version-{v}", f"variables-{s}-of-{S}.ckpt"), "wb").close()
+
+
+def test_checkpoint_prune_keeps_a_complete_version(tmp_path):
+    """Shard 0 prunes right after its own write: an incomplete newer version (another shard has not
+    written yet, or died) must not cost the last complete one (checkpoint.py)."""
+    from easydl_b200 import checkpoint as ck
+    d = str(tmp_path)
+    _touch_version(d, 10, range(4), 4)          # complete
+    _touch_version(d, 20, range(4), 4)          # complete
+    _touch_version(d, 30, [0], 4)               # shard 0 only: in progress / crashed
+    saver = ck.CheckpointSaver(d, keep_max=1)
+    saver.prune()
+    assert ck.list_versions(d) == [20, 30]      # 10 is behind the newest complete one; 20 survives
+    assert ck.latest_complete_version(d) == 20
+    _touch_version(d, 30, [1, 2, 3], 4)         # the other shards finish
+    saver.prune()
+    assert ck.list_versions(d) == [30]
+    assert ck.latest_complete_version(d) == 30
+
+
+def test_restore_skips_incomplete_versions(tmp_path):
+    from easydl_b200 import checkpoint as ck
+    import pytest as _pt
+    d = str(tmp_path)
+    _touch_version(d, 5, [0, 2], 3)
+    with _pt.raises(FileNotFoundError, match="no complete checkpoint"):
+        ck.latest_complete_version(d)
+    _touch_version(d, 3, range(3), 3)
+    assert ck.latest_complete_version(d) == 3
