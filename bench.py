@@ -51,6 +51,7 @@ def parse_args():
     ap.add_argument("--cpu-steps", type=int, default=3, help="timed oracle steps for cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="N>1: skip the oracle parity check before the warm-up")
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
     ap.add_argument("--force-sharded", action="store_true",
                     help="N=1 only: run the multi-shard code path (dedup/partition/exchange/expand) with S=1")
@@ -80,6 +81,37 @@ def algorithmic_bytes(N, U, D, optimizer):
     else:
         update = 4 * D * N + 4 * N + 24 * D * U
     return lookup, update
+
+
+NVLINK_GBS = 770.0   # measured peer copy per direction per GPU on this pool (B200_PROFILING.md); nominal 900
+
+
+def sharded_roofline(a, world, N, U, owner_counts, ms_step, peak, peak_kind):
+    """Per-rank byte counts of one sharded step (per GPU) against the two ceilings it can
+    hit: bytes that must leave the GPU over NVLink, and bytes that must cross its own HBM.  frac = the
+    larger of the two ideal times / the measured step time."""
+    D, S = a.dim, world
+    wire = 8 if a.wire == "f64" else 4
+    R, Uo = owner_counts            # keys received per owner, unique among them
+    out_frac = (S - 1) / S
+    nv = out_frac * (8 * U + 4 * D * R + wire * D * U)
+    hbm = (8 * N                                   # A: ids (the sort's working set stays in L2)
+           + 4 * D * R + 4 * D * R / S             # B: owner gather reads, local share of the writes
+           + 4 * D * U + 4 * D * N + 4 * N         # C: expand
+           + 4 * D * N + 4 * N + wire * D * U / S  # C: reduce, local share of the partial sums
+           + wire * D * R + (16 if a.optimizer == "adagrad" else 24) * D * Uo)   # D: owner reduce + update
+    t_nv, t_hbm = nv / (NVLINK_GBS * 1e9), hbm / (peak * 1e9)
+    bound = "nvlink" if t_nv >= t_hbm else "hbm"
+    t_step = ms_step * 1e-3
+    return {"kernel": "whole sharded step of one rank (slot exchange; NVLink-bound rounds and HBM-bound phases overlap "
+                      "only partly, so the ideal is the larger of the two)",
+            "bound": bound, "achieved": (nv if bound == "nvlink" else hbm) / t_step / 1e9,
+            "peak": NVLINK_GBS if bound == "nvlink" else peak, "unit": "GB/s",
+            "frac": max(t_nv, t_hbm) / t_step, "traffic": None, "peak_kind": peak_kind,
+            "nvlink_out_bytes_per_rank": nv, "hbm_bytes_per_rank": hbm,
+            "ideal_nvlink_ms": t_nv * 1e3, "ideal_hbm_ms": t_hbm * 1e3,
+            "nvlink_peak_note": "770 GB/s = measured peer copy per direction per GPU (B200_PROFILING.md); nominal 900",
+            "keys_received_per_owner": R, "unique_keys_per_owner": Uo}
 
 
 def measured_peak_gbs():
@@ -170,22 +202,45 @@ def cpu_reference(a, threads: int, steps: int, warmup: int):
     return a.batch * steps / dt, dt / steps
 
 
+def config_for(a, world, U_mean=None, sharded=False, nb=None):
+    """The `config` object of the JSON line: the same keys on both arms."""
+    F, D, B = N_FIELDS, a.dim, a.batch
+    N = B * F
+    table_gb = F * a.rows * D * 4 / 1e9
+    slots = 1 if a.optimizer == "adagrad" else 2
+    return {"workload": workload_name(a), "global_batch": B * world, "tables": F, "rows_per_table": a.rows,
+            "dim": D, "zipf_alpha": a.alpha, "optimizer": a.optimizer, "unique_per_step": U_mean,
+            "sharding": f"row-wise id mod {world}",
+            "code_path": "sharded" if sharded else "single-shard fused",
+            "gradient_wire": a.wire if sharded else None,
+            "exchange": (a.exchange if world > 1 else None),
+            "cache": f"inputs larger than L2: {table_gb * (1 + slots):.0f} GB of table + optimizer rows touched at "
+                     f"random, {nb if nb else a.n_batches} id batches cycled, {N * D * 4 / 1e6:.0f} MB gradient + "
+                     f"{N * D * 4 / 1e6:.0f} MB output per GPU per step"}
+
+
 def run_reference_arm(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     cores = os.cpu_count() or 1
     threads = min(cores, N_FIELDS)
-    steps = max(1, min(a.steps, 5))
-    warm = max(1, min(a.warmup, 1))
+    # honour --steps / --warmup as far as a bounded run allows: one probe step sizes the run to ~150 s
+    probe_v, probe_spp = cpu_reference(a, threads, 1, 1)
+    budget_s = 150.0
+    steps = max(1, min(a.steps, int(budget_s / max(probe_spp, 1e-3))))
+    warm = max(0, min(a.warmup, int(0.2 * budget_s / max(probe_spp, 1e-3))))
     v, spp = cpu_reference(a, threads, steps, warm)
     sample = (f"{steps} full steps (batch {a.batch}, {N_FIELDS} tables, dim {a.dim}) of the NumPy oracle, "
               f"one table per thread on {threads} threads, rows pre-materialised")
+    cfg = config_for(a, a.gpus, None, False, min(a.n_batches, 2))
+    cfg["code_path"] = "CPU parameter-server path (oracle port), one host, all cores; the GPUs are unused"
+    cfg["exchange"] = None
     line = {
         "metric": METRIC, "value": v, "unit": UNIT, "impl": "reference", "n_gpus": a.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": spp * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(a), "note": "CPU PS path; one host, all cores; the N GPUs are unused"},
+        "config": cfg,
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -219,6 +274,22 @@ def run_b200_arm(a):
     opt = OptimizerSpec.adagrad() if a.optimizer == "adagrad" else OptimizerSpec.adam()
     D, B, F = a.dim, a.batch, N_FIELDS
     N = B * F
+    if a.exchange == "auto":
+        a.exchange = "slots" if world > 1 else "peer"
+
+    # ---------------- real-rank parity against the oracle, before anything is timed (N > 1)
+    parity = None
+    if world > 1 and not a.no_parity:
+        from tools.parity import check_exchange
+        parity = check_exchange(a.exchange, dev, dist.group.WORLD,
+                                torch.float64 if a.wire == "f64" else torch.float32, a.lanes)
+        if not parity["ok"]:
+            if rank == 0:
+                print(json.dumps({"metric": METRIC, "error": "parity check against the oracle failed",
+                                  "parity": parity}), flush=True)
+            dist.destroy_process_group()
+            raise SystemExit(3)
+
     params = ShardParameters(rows, D, opt, world, rank, device=dev)
 
     sharded = world > 1 or a.force_sharded
@@ -229,8 +300,6 @@ def run_b200_arm(a):
         from easydl_b200.sharded_step import ShardedSparseStep
         from easydl_b200.exchange import PeerExchange, SingleExchange, TorchExchange
         wire_dtype = torch.float64 if a.wire == "f64" else torch.float32
-        if a.exchange == "auto":
-            a.exchange = "slots" if world > 1 else "peer"
         slots = world > 1 and a.exchange in ("slots", "slots-pipe")
         if slots:
             ex = None
@@ -274,7 +343,7 @@ def run_b200_arm(a):
     if not sharded and not a.no_graph:
         from easydl_b200.step import GraphedStep
         graphed = [GraphedStep(step, ids_dev[i], grad_dev) for i in range(nb)]
-    elif sharded and world > 1 and a.exchange in ("slots", "slots-pipe") and a.optimizer == "adagrad" and not a.no_graph:
+    elif sharded and world > 1 and a.exchange in ("slots", "slots-pipe") and not a.no_graph:
         from easydl_b200.slot_step import GraphedSlotStep
         graphed = [GraphedSlotStep(step, ids_dev[i], grad_dev) for i in range(nb)]
 
@@ -354,6 +423,34 @@ def run_b200_arm(a):
                   "update_ms": statistics.mean(up),
                   "phase_loop_ms_per_step": p_begin.elapsed_time(p_end) / a.steps}
 
+    sharded_phases, owner_counts = None, None
+    if sharded and world > 1 and a.exchange == "slots":
+        # the same step issued eagerly, phases in a row on one stream (no helper-stream overlap), a CUDA
+        # event after each: says where the time goes; the headline above is the overlapped graph replay
+        acc = {n: 0.0 for n in step.PHASES}
+        for i in range(3):
+            step.run_timed(ids_dev[i % nb], grad_dev)
+        barrier()
+        k_ph = min(a.steps, 20)
+        for i in range(k_ph):
+            marks = step.run_timed(ids_dev[(a.warmup + i) % nb], grad_dev)
+            torch.cuda.synchronize()
+            for n, e0, e1 in marks:
+                acc[n] += e0.elapsed_time(e1)
+        step.check()
+        t_ph = torch.tensor([acc[n] / k_ph for n in step.PHASES], dtype=torch.float64, device=dev)
+        dist.all_reduce(t_ph, op=dist.ReduceOp.MAX)
+        sharded_phases = {n + "_ms": float(t_ph[j].item()) for j, n in enumerate(step.PHASES)}
+        oc = torch.stack([step.n_recv[0].to(torch.float64), step.uq2.n_unique[0].to(torch.float64)])
+        dist.all_reduce(oc, op=dist.ReduceOp.SUM)
+        owner_counts = (float(oc[0].item()) / world, float(oc[1].item()) / world)   # received keys, owner-unique keys
+    elif sharded and world > 1 and a.exchange == "slots-pipe":
+        torch.cuda.synchronize()
+        oc = torch.stack([sum(l.n_recv[0].to(torch.float64) for l in step.lanes),
+                          sum(l.uq2.n_unique[0].to(torch.float64) for l in step.lanes)])
+        dist.all_reduce(oc, op=dist.ReduceOp.SUM)
+        owner_counts = (float(oc[0].item()) / world, float(oc[1].item()) / world)
+
     # ---------------- end-to-end through the host-buffer PS API
     e2e = None
     if not a.no_e2e:
@@ -390,14 +487,7 @@ def run_b200_arm(a):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": ms_max / a.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(a), "global_batch": B * world,
-                       "tables": F, "rows_per_table": a.rows, "dim": D, "zipf_alpha": a.alpha,
-                       "unique_per_step": U_mean, "sharding": f"row-wise id mod {world}",
-                       "code_path": "sharded" if sharded else "single-shard fused",
-                       "gradient_wire": a.wire if sharded else None,
-                       "exchange": (a.exchange if world > 1 else None),
-                       "cache": "inputs larger than L2: 133 GB of table rows touched at random, "
-                                f"{nb} id batches cycled, 436 MB gradient + 436 MB output per step"},
+            "config": config_for(a, world, U_mean, sharded, nb),
             "gpu_launches": step.launches_per_step * a.steps,
             "launch_mode": "cuda_graph" if graphed is not None else "eager",
             "clocks": clocks,
@@ -412,7 +502,7 @@ def run_b200_arm(a):
             t_lk = phases["lookup_ms"] * 1e-3
             ach = update_b / t_up / 1e9
             line["roofline"] = {
-                "kernel": "k_seg_classify + k_seg_direct || (k_seg_chunk + k_seg_long_final) (segmented reduce + "
+                "kernel": "k_seg_stream || (k_seg_classify -> k_seg_chunk -> k_seg_long_final) (segmented reduce + "
                           "row update: four launches per step, hot-id kernels on a forked branch, timed together)",
                 "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": traffic, "traffic_source": traffic_src, "peak_kind": peak_kind,
@@ -422,6 +512,12 @@ def run_b200_arm(a):
             line["phases"]["lookup_gbs"] = lookup_b / t_lk / 1e9
             line["phases"]["lookup_frac"] = lookup_b / t_lk / 1e9 / peak
             line["phases"]["lookup_update_gbs_whole_step"] = (lookup_b + update_b) / (ms_max / a.steps * 1e-3) / 1e9
+        if parity is not None:
+            line["parity"] = parity
+        if sharded_phases is not None:
+            line["phases"] = sharded_phases
+        if owner_counts is not None:
+            line["roofline"] = sharded_roofline(a, world, N, U_mean, owner_counts, ms_max / a.steps, peak, peak_kind)
         if e2e:
             line["e2e"] = e2e
         if not a.no_cpu_baseline:

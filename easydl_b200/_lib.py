@@ -36,30 +36,32 @@ PROTOTYPES = {
     "edl_last_error_string": (C.c_char_p, []),
     "edl_tuning_set": (_int, [C.c_char_p, _int]),
     "edl_tuning_get": (_int, [C.c_char_p, C.POINTER(C.c_int)]),
-    "edl_init_rows": (_int, [_p, _int, _p, _i64, _i64, C.c_uint64, _p]),
+    "edl_init_rows": (_int, [_p, _int, _i64, _p, _i64, _i64, C.c_uint64, _p]),
     "edl_fill_f32": (_int, [_p, _i64, C.c_float, _p]),
+    "edl_fill_rows_f32": (_int, [_p, _int, _i64, _i64, C.c_float, _p]),
     "edl_unique_workspace_bytes": (_sz, [_i64, _int, _int, _int]),
     "edl_unique": (_int, [_p, _i64, _p, _p, _int, _int, _int, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "edl_unique_static": (_int, [_p, _i64, _p, _p, _int, _int, _int, _p, _p, _p, _p, _p, _p, _p, _p]),
     "edl_partition_mod_workspace_bytes": (_sz, [_i64, _int]),
     "edl_partition_mod": (_int, [_p, _i64, _p, _p, _int, _p, _p, _p, _p, _p, _sz, _p]),
-    "edl_gather_keys": (_int, [_p, _int, _p, _i64, _p, _p, _p, _p]),
-    "edl_gather_ids": (_int, [_p, _int, _p, _i64, _p, _int, _p, _p]),
+    "edl_gather_keys": (_int, [_p, _int, _i64, _p, _i64, _p, _p, _p, _p]),
+    "edl_gather_ids": (_int, [_p, _int, _i64, _p, _i64, _p, _int, _p, _p]),
     "edl_expand": (_int, [_p, _int, _p, _i64, _p, _p]),
     "edl_compose_index": (_int, [_p, _p, _i64, _p, _p]),
     "edl_segreduce_workspace_bytes": (_sz, [_i64, _i64, _int]),
     "edl_segreduce": (_int, [_p, _int, _p, _p, _p, _p, _i64, _i64, _p, _p, _int, _p, _p, _sz, _p]),
-    "edl_segreduce_update": (_int, [_p, _p, _p, _int, _p, _p, _p, _p, _p, _i64, _i64, _p, _int, _p,
+    "edl_segreduce_update": (_int, [_p, _p, _p, _int, _i64, _p, _p, _p, _p, _p, _i64, _i64, _p, _int, _p,
                                     C.POINTER(OptParams), _p, _p, _sz, _p]),
+    "edl_selftest_rounding": (_int, [_i64, C.c_uint64, _p, _p]),
     "edl_export_workspace_bytes": (_sz, [_i64]),
     "edl_export_count": (_int, [_p, _i64, _p, _p, _sz, _p]),
-    "edl_export_shard": (_int, [_p, _p, _p, _int, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _sz, _p]),
-    "edl_import_shard": (_int, [_p, _p, _p, _int, _p, _p, _p, _p, _p, _p, _i64, _p]),
-    "edl_scatter_rows": (_int, [_p, _int, _p, _i64, _p, _p, _p]),
+    "edl_export_shard": (_int, [_p, _p, _p, _int, _i64, _p, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "edl_import_shard": (_int, [_p, _p, _p, _int, _i64, _p, _p, _p, _p, _p, _p, _i64, _p]),
+    "edl_scatter_rows": (_int, [_p, _int, _p, _i64, _p, _p, _i64, _p]),
     "edl_lazy_index_bytes": (_sz, [_i64]),
     "edl_lazy_clear": (_int, [_p, _i64, _p]),
-    "edl_lazy_gather": (_int, [_p, _i64, _p, _int, _p, _i64, _p, _p, C.c_uint64, _p, _p]),
-    "edl_lazy_insert": (_int, [_p, _i64, _p, _p, _p, _int, _i64, _p, _i64, _p, _p, C.c_uint64,
+    "edl_lazy_gather": (_int, [_p, _i64, _p, _int, _i64, _p, _i64, _p, _p, C.c_uint64, _p, _p]),
+    "edl_lazy_insert": (_int, [_p, _i64, _p, _p, _p, _int, _i64, _i64, _p, _i64, _p, _p, C.c_uint64,
                                C.c_float, C.c_float, _p, _p]),
     "edl_lazy_status_ptr": (_p, [_p, _i64]),
     "edl_lazy_dump": (_int, [_p, _i64, _p, _p, _p]),

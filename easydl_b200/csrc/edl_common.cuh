@@ -21,7 +21,7 @@ enum EdlTune {
   EDL_TUNE_STREAM_CTAS,    // k_seg_stream: persistent CTAs per SM
   EDL_TUNE_GATHER_IMPL,    // 0: k_gather, 1: k_gather_pf (row index of the next iteration prefetched)
   EDL_TUNE_CLASSIFY_SIDE,  // forked update: 1 = k_seg_classify on the helper stream too
-  EDL_TUNE_SORT_IMPL,      // reserved
+  EDL_TUNE_STREAM_STAGES,  // k_seg_stream: ring slots in use (2..4)
   EDL_TUNE_COUNT
 };
 int edl_tune(int id);
@@ -51,6 +51,18 @@ int edl_tune(int id);
       return EDL_ECUDA;                                                             \
     }                                                                               \
   } while (0)
+
+// Row stride of a table / slot array in floats: 0 = dense rows (stride == dim).  Parameter and
+// optimizer-slot rows of one id may be stored side by side in one record ([p | slot0 | slot1], stride
+// (1 + n_slots) * dim, slot pointers offset by dim): one DRAM page and one TLB entry per id instead of
+// one per array.  -> stride in float4 units.
+static inline int edl_row_stride4(const char* who, int dim, int64_t row_stride, int* out) {
+  if (row_stride == 0) row_stride = dim;
+  EDL_REQUIRE(row_stride >= dim && row_stride % 4 == 0 && row_stride < (1 << 20), EDL_EINVAL,
+              "%s: row_stride=%lld must be 0 or a multiple of 4 that is >= dim=%d", who, (long long)row_stride, dim);
+  *out = (int)(row_stride / 4);
+  return EDL_OK;
+}
 
 static inline size_t edl_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 static inline int64_t edl_cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }

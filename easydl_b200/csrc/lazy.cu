@@ -55,7 +55,7 @@ __device__ __forceinline__ long long probe(const long long* __restrict__ idx_key
 template <int kD4>
 __global__ void __launch_bounds__(kThreads, 6)
 k_lazy_gather(const long long* __restrict__ idx_keys, const int* __restrict__ idx_slot,
-              unsigned long long mask, const float4* __restrict__ slab, int D4_rt,
+              unsigned long long mask, const float4* __restrict__ slab, int D4_rt, int RS4,
               const int64_t* __restrict__ keys, int64_t n, const int32_t* n_dev,
               const int64_t* __restrict__ layout, unsigned long long seed, float4* __restrict__ out) {
   __shared__ EdlLayoutSmem L;
@@ -70,7 +70,7 @@ k_lazy_gather(const long long* __restrict__ idx_keys, const int* __restrict__ id
     const int c = (int)(e - i * D4);
     const long long key = keys[i];
     const long long slot = probe(idx_keys, idx_slot, mask, key);
-    out[e] = slot >= 0 ? slab[slot * D4 + c] : init_row4(&L, key, D4, c, seed);
+    out[e] = slot >= 0 ? slab[slot * RS4 + c] : init_row4(&L, key, D4, c, seed);
   }
 }
 
@@ -118,7 +118,7 @@ k_lazy_insert(long long* __restrict__ idx_keys, int* __restrict__ idx_slot, unsi
 
 // initialise the rows claimed by k_lazy_insert and strip the marker bit
 __global__ void __launch_bounds__(kThreads)
-k_lazy_init_new(float4* __restrict__ slab, float4* __restrict__ slot0, float4* __restrict__ slot1, int D4,
+k_lazy_init_new(float4* __restrict__ slab, float4* __restrict__ slot0, float4* __restrict__ slot1, int D4, int RS4,
                 const int64_t* __restrict__ keys, int64_t* __restrict__ slots, int64_t n, const int32_t* n_dev,
                 const int64_t* __restrict__ layout, unsigned long long seed, float init0, float init1) {
   __shared__ EdlLayoutSmem L;
@@ -133,9 +133,9 @@ k_lazy_init_new(float4* __restrict__ slab, float4* __restrict__ slot0, float4* _
     const long long s = slots[i];
     if (s >= 0 && (s & (1ll << 62))) {
       const long long row = s & ~(1ll << 62);
-      slab[row * D4 + c] = init_row4(&L, keys[i], D4, c, seed);
-      if (slot0) slot0[row * D4 + c] = make_float4(init0, init0, init0, init0);
-      if (slot1) slot1[row * D4 + c] = make_float4(init1, init1, init1, init1);
+      slab[row * RS4 + c] = init_row4(&L, keys[i], D4, c, seed);
+      if (slot0) slot0[row * RS4 + c] = make_float4(init0, init0, init0, init0);
+      if (slot1) slot1[row * RS4 + c] = make_float4(init1, init1, init1, init1);
     }
   }
 }
@@ -199,20 +199,22 @@ extern "C" int edl_lazy_clear(void* index, int64_t index_capacity, edl_stream_t 
 }
 
 extern "C" int edl_lazy_gather(const void* index, int64_t index_capacity, const float* slab, int dim,
-                               const int64_t* keys, int64_t n, const int32_t* n_dev, const int64_t* layout,
+                               int64_t row_stride, const int64_t* keys, int64_t n, const int32_t* n_dev, const int64_t* layout,
                                uint64_t seed, float* out, edl_stream_t stream) {
   EDL_REQUIRE(dim > 0 && dim % 4 == 0, EDL_EINVAL, "edl_lazy_gather: dim=%d must be a positive multiple of 4", dim);
   EDL_REQUIRE(n >= 0, EDL_EINVAL, "edl_lazy_gather: n negative");
+  int RS4 = 0;
+  { int rc0 = edl_row_stride4("edl_lazy_gather", dim, row_stride, &RS4); if (rc0) return rc0; }
   if (n == 0) return EDL_OK;
   EDL_REQUIRE(index && pow2(index_capacity) && slab && keys && out && layout, EDL_EINVAL, "edl_lazy_gather: null pointer");
   LazyIdx I = carve_idx((void*)index, index_capacity);
   const int D4 = dim / 4;
   const int g = grid_for(n * D4);
   cudaStream_t st = (cudaStream_t)stream;
-#define EDL_CASE(W) case W: k_lazy_gather<W><<<g, kThreads, 0, st>>>(I.keys, I.slots, (unsigned long long)index_capacity - 1, (const float4*)slab, D4, keys, n, n_dev, layout, seed, (float4*)out); break;
+#define EDL_CASE(W) case W: k_lazy_gather<W><<<g, kThreads, 0, st>>>(I.keys, I.slots, (unsigned long long)index_capacity - 1, (const float4*)slab, D4, RS4, keys, n, n_dev, layout, seed, (float4*)out); break;
   switch (D4) {
     EDL_CASE(4) EDL_CASE(8) EDL_CASE(16) EDL_CASE(32) EDL_CASE(64)
-    default: k_lazy_gather<0><<<g, kThreads, 0, st>>>(I.keys, I.slots, (unsigned long long)index_capacity - 1, (const float4*)slab, D4, keys, n, n_dev, layout, seed, (float4*)out);
+    default: k_lazy_gather<0><<<g, kThreads, 0, st>>>(I.keys, I.slots, (unsigned long long)index_capacity - 1, (const float4*)slab, D4, RS4, keys, n, n_dev, layout, seed, (float4*)out);
   }
 #undef EDL_CASE
   EDL_LAUNCH_CHECK("k_lazy_gather");
@@ -220,11 +222,13 @@ extern "C" int edl_lazy_gather(const void* index, int64_t index_capacity, const 
 }
 
 extern "C" int edl_lazy_insert(void* index, int64_t index_capacity, float* slab, float* slot0, float* slot1,
-                               int dim, int64_t max_rows, const int64_t* keys, int64_t n, const int32_t* n_dev,
+                               int dim, int64_t row_stride, int64_t max_rows, const int64_t* keys, int64_t n, const int32_t* n_dev,
                                const int64_t* layout, uint64_t seed, float slot0_init, float slot1_init,
                                int64_t* slots_out, edl_stream_t stream) {
   EDL_REQUIRE(dim > 0 && dim % 4 == 0, EDL_EINVAL, "edl_lazy_insert: dim=%d must be a positive multiple of 4", dim);
   EDL_REQUIRE(n >= 0 && max_rows > 0 && max_rows < 0x7fffffff, EDL_EINVAL, "edl_lazy_insert: bad sizes");
+  int RS4 = 0;
+  { int rc0 = edl_row_stride4("edl_lazy_insert", dim, row_stride, &RS4); if (rc0) return rc0; }
   if (n == 0) return EDL_OK;
   EDL_REQUIRE(index && pow2(index_capacity) && slab && keys && slots_out && layout, EDL_EINVAL, "edl_lazy_insert: null pointer");
   EDL_REQUIRE(index_capacity >= 2 * max_rows, EDL_EINVAL, "edl_lazy_insert: index capacity must be >= 2 x max_rows");
@@ -233,7 +237,7 @@ extern "C" int edl_lazy_insert(void* index, int64_t index_capacity, float* slab,
   const int D4 = dim / 4;
   k_lazy_insert<<<grid_for(n), kThreads, 0, st>>>(I.keys, I.slots, (unsigned long long)index_capacity - 1, keys, n,
                                                   n_dev, I.count, (int)max_rows, slots_out, I.err);
-  k_lazy_init_new<<<grid_for(n * D4), kThreads, 0, st>>>((float4*)slab, (float4*)slot0, (float4*)slot1, D4, keys,
+  k_lazy_init_new<<<grid_for(n * D4), kThreads, 0, st>>>((float4*)slab, (float4*)slot0, (float4*)slot1, D4, RS4, keys,
                                                         slots_out, n, n_dev, layout, seed, slot0_init, slot1_init);
   k_lazy_strip<<<grid_for(n), kThreads, 0, st>>>(slots_out, n, n_dev, (long long)max_rows);
   EDL_LAUNCH_CHECK("lazy insert kernels");

@@ -120,7 +120,7 @@ k_enumerate(const uint32_t* __restrict__ touched, int64_t n_rows, const uint32_t
 
 __global__ void __launch_bounds__(kThreads)
 k_copy_rows(const float4* __restrict__ slab, const float4* __restrict__ s0, const float4* __restrict__ s1,
-            int D4, const int64_t* __restrict__ rows_idx, const int32_t* __restrict__ n_dev,
+            int D4, int RS4, const int64_t* __restrict__ rows_idx, const int32_t* __restrict__ n_dev,
             int64_t capacity, float4* __restrict__ rows_out, float4* __restrict__ s0_out,
             float4* __restrict__ s1_out) {
   int64_t n = *n_dev;
@@ -130,7 +130,7 @@ k_copy_rows(const float4* __restrict__ slab, const float4* __restrict__ s0, cons
        e += (int64_t)gridDim.x * kThreads) {
     int64_t i = e / D4;
     int c = (int)(e - i * D4);
-    int64_t src = rows_idx[i] * D4 + c;
+    int64_t src = rows_idx[i] * RS4 + c;
     rows_out[e] = slab[src];
     if (s0_out) s0_out[e] = s0[src];
     if (s1_out) s1_out[e] = s1[src];
@@ -156,7 +156,7 @@ k_rows_to_keys(int64_t* __restrict__ keys, const int32_t* __restrict__ n_dev, in
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_import(float4* __restrict__ slab, float4* __restrict__ s0, float4* __restrict__ s1, int D4,
+k_import(float4* __restrict__ slab, float4* __restrict__ s0, float4* __restrict__ s1, int D4, int RS4,
          uint32_t* __restrict__ touched, const int64_t* __restrict__ layout,
          const int64_t* __restrict__ keys, const float4* __restrict__ rows,
          const float4* __restrict__ s0_in, const float4* __restrict__ s1_in, int64_t n) {
@@ -177,7 +177,7 @@ k_import(float4* __restrict__ slab, float4* __restrict__ s0, float4* __restrict_
       if (id % L.S != L.shard) continue;  // another shard's record
       row = L.lb[t] + (long long)(id / L.S);
     }
-    int64_t dst = row * D4 + c;
+    int64_t dst = row * RS4 + c;
     slab[dst] = rows[e];
     if (s0_in) s0[dst] = s0_in[e];
     if (s1_in) s1[dst] = s1_in[e];
@@ -220,12 +220,14 @@ extern "C" int edl_export_count(const uint32_t* touched, int64_t n_rows, int32_t
 }
 
 extern "C" int edl_export_shard(const float* slab, const float* slot0, const float* slot1, int dim,
-                                const uint32_t* touched, int64_t n_rows, const int64_t* layout,
+                                int64_t row_stride, const uint32_t* touched, int64_t n_rows, const int64_t* layout,
                                 int64_t capacity, int64_t* keys_out, float* rows_out,
                                 float* slot0_out, float* slot1_out, int32_t* n_out, void* workspace,
                                 size_t workspace_bytes, edl_stream_t stream) {
   EDL_REQUIRE(dim > 0 && dim % 4 == 0, EDL_EINVAL, "edl_export_shard: dim=%d must be a positive multiple of 4", dim);
   EDL_REQUIRE(capacity >= 0, EDL_EINVAL, "edl_export_shard: capacity negative");
+  int RS4 = 0;
+  { int rc0 = edl_row_stride4("edl_export_shard", dim, row_stride, &RS4); if (rc0) return rc0; }
   int rc = edl_export_count(touched, n_rows, n_out, workspace, workspace_bytes, stream);
   if (rc) return rc;
   if (n_rows == 0 || capacity == 0) return EDL_OK;
@@ -237,26 +239,28 @@ extern "C" int edl_export_shard(const float* slab, const float* slot0, const flo
   const int D4 = dim / 4;
   k_enumerate<<<tiles, kThreads, 0, st>>>(touched, n_rows, (const uint32_t*)workspace, capacity, keys_out);
   k_copy_rows<<<grid_for(capacity * D4), kThreads, 0, st>>>(
-      (const float4*)slab, (const float4*)slot0, (const float4*)slot1, D4, keys_out, n_out, capacity,
+      (const float4*)slab, (const float4*)slot0, (const float4*)slot1, D4, RS4, keys_out, n_out, capacity,
       (float4*)rows_out, (float4*)slot0_out, (float4*)slot1_out);
   k_rows_to_keys<<<grid_for(capacity), kThreads, 0, st>>>(keys_out, n_out, capacity, layout);
   EDL_LAUNCH_CHECK("export kernels");
   return EDL_OK;
 }
 
-extern "C" int edl_import_shard(float* slab, float* slot0, float* slot1, int dim, uint32_t* touched,
+extern "C" int edl_import_shard(float* slab, float* slot0, float* slot1, int dim, int64_t row_stride, uint32_t* touched,
                                 const int64_t* layout, const int64_t* keys, const float* rows,
                                 const float* slot0_in, const float* slot1_in, int64_t n,
                                 edl_stream_t stream) {
   EDL_REQUIRE(dim > 0 && dim % 4 == 0, EDL_EINVAL, "edl_import_shard: dim=%d must be a positive multiple of 4", dim);
   EDL_REQUIRE(n >= 0, EDL_EINVAL, "edl_import_shard: n negative");
+  int RS4 = 0;
+  { int rc0 = edl_row_stride4("edl_import_shard", dim, row_stride, &RS4); if (rc0) return rc0; }
   if (n == 0) return EDL_OK;
   EDL_REQUIRE(slab && keys && rows, EDL_EINVAL, "edl_import_shard: null pointer");
   EDL_REQUIRE(!slot0_in || slot0, EDL_EINVAL, "edl_import_shard: slot0_in without slot0");
   EDL_REQUIRE(!slot1_in || slot1, EDL_EINVAL, "edl_import_shard: slot1_in without slot1");
   const int D4 = dim / 4;
   k_import<<<grid_for(n * D4), kThreads, 0, (cudaStream_t)stream>>>(
-      (float4*)slab, (float4*)slot0, (float4*)slot1, D4, touched, layout, keys, (const float4*)rows,
+      (float4*)slab, (float4*)slot0, (float4*)slot1, D4, RS4, touched, layout, keys, (const float4*)rows,
       (const float4*)slot0_in, (const float4*)slot1_in, n);
   EDL_LAUNCH_CHECK("k_import");
   return EDL_OK;

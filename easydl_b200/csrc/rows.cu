@@ -31,7 +31,7 @@ __device__ __forceinline__ float init_value(unsigned long long salt, unsigned lo
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_init_rows(float4* __restrict__ slab, int D4, const int64_t* __restrict__ layout, int64_t row_begin,
+k_init_rows(float4* __restrict__ slab, int D4, int RS4, const int64_t* __restrict__ layout, int64_t row_begin,
             int64_t n_rows, unsigned long long seed) {
   __shared__ EdlLayoutSmem L;
   edl_layout_load(&L, layout);
@@ -51,7 +51,18 @@ k_init_rows(float4* __restrict__ slab, int D4, const int64_t* __restrict__ layou
     v.y = init_value(salt, idx + 1);
     v.z = init_value(salt, idx + 2);
     v.w = init_value(salt, idx + 3);
-    slab[row * D4 + c4] = v;
+    slab[row * RS4 + c4] = v;
+  }
+}
+
+// value fill of `dim`-wide rows that lie `RS4` float4 apart (optimizer slots inside interleaved records)
+__global__ void __launch_bounds__(kThreads)
+k_fill_rows(float4* __restrict__ dst, int D4, int RS4, int64_t n_rows, float value) {
+  const float4 v = make_float4(value, value, value, value);
+  const int64_t total = n_rows * D4;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = e / D4;
+    dst[r * RS4 + (e - r * D4)] = v;
   }
 }
 
@@ -104,7 +115,7 @@ struct IndexRowFn {  // int32 index (expand by `inverse`, permute by `perm`)
 // kD4 > 0: compile-time row width in float4 (power of two); kD4 == 0: runtime width.
 template <int kD4, typename RowFn, bool kUseLayout>
 __global__ void __launch_bounds__(kThreads, 8)
-k_gather(const float4* __restrict__ src, int D4_rt, RowFn fn, int64_t n, const int32_t* n_dev,
+k_gather(const float4* __restrict__ src, int D4_rt, int S4, RowFn fn, int64_t n, const int32_t* n_dev,
          const int64_t* __restrict__ layout, float4* __restrict__ out) {
   __shared__ EdlLayoutSmem L;
   if (kUseLayout) {
@@ -132,7 +143,7 @@ k_gather(const float4* __restrict__ src, int D4_rt, RowFn fn, int64_t n, const i
 #pragma unroll
     for (int k = 0; k < kUnroll; ++k) {
       int64_t e = e0 + k * stride;
-      if (e < total) v[k] = src[r[k] * D4 + c[k]];
+      if (e < total) v[k] = src[r[k] * S4 + c[k]];
     }
 #pragma unroll
     for (int k = 0; k < kUnroll; ++k) {
@@ -148,7 +159,7 @@ k_gather(const float4* __restrict__ src, int D4_rt, RowFn fn, int64_t n, const i
 // For power-of-two row widths that divide the CTA the column of a thread is fixed (c = tid mod D4).
 template <int kD4, typename RowFn, bool kUseLayout>
 __global__ void __launch_bounds__(kThreads, 8)
-k_gather_pf(const float4* __restrict__ src, int D4_rt, RowFn fn, int64_t n, const int32_t* n_dev,
+k_gather_pf(const float4* __restrict__ src, int D4_rt, int S4, RowFn fn, int64_t n, const int32_t* n_dev,
             const int64_t* __restrict__ layout, float4* __restrict__ out) {
   __shared__ EdlLayoutSmem L;
   if (kUseLayout) {
@@ -178,7 +189,7 @@ k_gather_pf(const float4* __restrict__ src, int D4_rt, RowFn fn, int64_t n, cons
 #pragma unroll
     for (int k = 0; k < kUnroll; ++k) {
       const int64_t e = e0 + k * stride;
-      if (e < total) v[k] = src[r[k] * D4 + (int)(e % D4)];
+      if (e < total) v[k] = src[r[k] * S4 + (int)(e % D4)];
     }
 #pragma unroll
     for (int k = 0; k < kUnroll; ++k) {
@@ -229,7 +240,7 @@ k_expand_window(const float4* __restrict__ src, int D4_rt, const int32_t* __rest
 // scatter form: out[pos[i]] = rows[i]
 template <int kD4>
 __global__ void __launch_bounds__(kThreads)
-k_scatter_rows(const float4* __restrict__ rows, int D4_rt, const int32_t* __restrict__ pos, int64_t n,
+k_scatter_rows(const float4* __restrict__ rows, int D4_rt, int OS4, const int32_t* __restrict__ pos, int64_t n,
                const int32_t* n_dev, float4* __restrict__ out) {
   const int D4 = kD4 > 0 ? kD4 : D4_rt;
   int64_t ne = n;
@@ -239,7 +250,7 @@ k_scatter_rows(const float4* __restrict__ rows, int D4_rt, const int32_t* __rest
        e += (int64_t)gridDim.x * kThreads) {
     int64_t i = e / D4;
     int c = (int)(e - i * D4);
-    out[(int64_t)pos[i] * D4 + c] = edl_ld_cs(rows + e);
+    out[(int64_t)pos[i] * OS4 + c] = edl_ld_cs(rows + e);
   }
 }
 
@@ -260,30 +271,33 @@ int grid_for(int64_t elems, int per_thread) {
 }
 
 template <typename RowFn, bool kUseLayout>
-int launch_gather(const float* src, int dim, RowFn fn, int64_t n, const int32_t* n_dev,
+int launch_gather(const float* src, int dim, int64_t row_stride, RowFn fn, int64_t n, const int32_t* n_dev,
                   const int64_t* layout, float* out, cudaStream_t st, const char* who) {
   EDL_REQUIRE(dim > 0 && dim % 4 == 0, EDL_EINVAL, "%s: dim=%d must be a positive multiple of 4", who, dim);
+  int S4 = 0;
+  { int rc0 = edl_row_stride4(who, dim, row_stride, &S4); if (rc0) return rc0; }
   EDL_REQUIRE(n >= 0, EDL_EINVAL, "%s: n=%lld negative", who, (long long)n);
   if (n == 0) return EDL_OK;
   EDL_REQUIRE(src && out, EDL_EINVAL, "%s: null pointer", who);
   EDL_REQUIRE((((uintptr_t)src | (uintptr_t)out) & 15) == 0, EDL_EINVAL, "%s: rows must be 16-byte aligned", who);
   const int D4 = dim / 4;
   const int g = grid_for(n * D4, kUnroll);
+  const size_t pad = 0;
   const float4* s4 = (const float4*)src;
   float4* o4 = (float4*)out;
   if (edl_tune(EDL_TUNE_GATHER_IMPL) == 1) {
     switch (D4) {
-#define EDL_CASE(W) case W: k_gather_pf<W, RowFn, kUseLayout><<<g, kThreads, 0, st>>>(s4, D4, fn, n, n_dev, layout, o4); break;
+#define EDL_CASE(W) case W: k_gather_pf<W, RowFn, kUseLayout><<<g, kThreads, pad, st>>>(s4, D4, S4, fn, n, n_dev, layout, o4); break;
       EDL_CASE(4) EDL_CASE(8) EDL_CASE(16) EDL_CASE(32) EDL_CASE(64)
 #undef EDL_CASE
-      default: k_gather_pf<0, RowFn, kUseLayout><<<g, kThreads, 0, st>>>(s4, D4, fn, n, n_dev, layout, o4);
+      default: k_gather_pf<0, RowFn, kUseLayout><<<g, kThreads, pad, st>>>(s4, D4, S4, fn, n, n_dev, layout, o4);
     }
   } else {
     switch (D4) {
-#define EDL_CASE(W) case W: k_gather<W, RowFn, kUseLayout><<<g, kThreads, 0, st>>>(s4, D4, fn, n, n_dev, layout, o4); break;
+#define EDL_CASE(W) case W: k_gather<W, RowFn, kUseLayout><<<g, kThreads, pad, st>>>(s4, D4, S4, fn, n, n_dev, layout, o4); break;
       EDL_CASE(4) EDL_CASE(8) EDL_CASE(16) EDL_CASE(32) EDL_CASE(64)
 #undef EDL_CASE
-      default: k_gather<0, RowFn, kUseLayout><<<g, kThreads, 0, st>>>(s4, D4, fn, n, n_dev, layout, o4);
+      default: k_gather<0, RowFn, kUseLayout><<<g, kThreads, pad, st>>>(s4, D4, S4, fn, n, n_dev, layout, o4);
     }
   }
   EDL_LAUNCH_CHECK(who);
@@ -292,16 +306,18 @@ int launch_gather(const float* src, int dim, RowFn fn, int64_t n, const int32_t*
 
 }  // namespace
 
-extern "C" int edl_init_rows(float* slab, int dim, const int64_t* layout, int64_t row_begin,
+extern "C" int edl_init_rows(float* slab, int dim, int64_t row_stride, const int64_t* layout, int64_t row_begin,
                              int64_t n_rows, uint64_t seed, edl_stream_t stream) {
   EDL_REQUIRE(dim > 0 && dim % 4 == 0, EDL_EINVAL, "edl_init_rows: dim=%d must be a positive multiple of 4", dim);
+  int RS4 = 0;
+  { int rc0 = edl_row_stride4("edl_init_rows", dim, row_stride, &RS4); if (rc0) return rc0; }
   EDL_REQUIRE(layout, EDL_EINVAL, "edl_init_rows: layout is required (tables are located through local_base)");
   EDL_REQUIRE(row_begin >= 0 && n_rows >= 0, EDL_EINVAL, "edl_init_rows: negative range");
   if (n_rows == 0) return EDL_OK;
   EDL_REQUIRE(slab && (((uintptr_t)slab) & 15) == 0, EDL_EINVAL, "edl_init_rows: slab null or misaligned");
   const int D4 = dim / 4;
   const int g = grid_for(n_rows * D4, 1);
-  k_init_rows<<<g, kThreads, 0, (cudaStream_t)stream>>>((float4*)slab, D4, layout, row_begin, n_rows, seed);
+  k_init_rows<<<g, kThreads, 0, (cudaStream_t)stream>>>((float4*)slab, D4, RS4, layout, row_begin, n_rows, seed);
   EDL_LAUNCH_CHECK("k_init_rows");
   return EDL_OK;
 }
@@ -315,16 +331,28 @@ extern "C" int edl_fill_f32(float* dst, int64_t n, float value, edl_stream_t str
   return EDL_OK;
 }
 
-extern "C" int edl_gather_keys(const float* slab, int dim, const int64_t* keys, int64_t n,
+extern "C" int edl_fill_rows_f32(float* dst, int dim, int64_t row_stride, int64_t n_rows, float value,
+                                 edl_stream_t stream) {
+  EDL_REQUIRE(dim > 0 && dim % 4 == 0 && n_rows >= 0, EDL_EINVAL, "edl_fill_rows_f32: bad dim / n_rows");
+  int RS4 = 0;
+  { int rc0 = edl_row_stride4("edl_fill_rows_f32", dim, row_stride, &RS4); if (rc0) return rc0; }
+  if (n_rows == 0) return EDL_OK;
+  EDL_REQUIRE(dst && (((uintptr_t)dst) & 15) == 0, EDL_EINVAL, "edl_fill_rows_f32: dst null or misaligned");
+  k_fill_rows<<<grid_for(n_rows * (dim / 4), 1), kThreads, 0, (cudaStream_t)stream>>>((float4*)dst, dim / 4, RS4, n_rows, value);
+  EDL_LAUNCH_CHECK("k_fill_rows");
+  return EDL_OK;
+}
+
+extern "C" int edl_gather_keys(const float* slab, int dim, int64_t row_stride, const int64_t* keys, int64_t n,
                                const int32_t* n_dev, const int64_t* layout, float* out,
                                edl_stream_t stream) {
   EDL_REQUIRE(n == 0 || keys, EDL_EINVAL, "edl_gather_keys: keys is null");
   KeyRowFn fn{keys};
-  return launch_gather<KeyRowFn, true>(slab, dim, fn, n, n_dev, layout, out, (cudaStream_t)stream,
+  return launch_gather<KeyRowFn, true>(slab, dim, row_stride, fn, n, n_dev, layout, out, (cudaStream_t)stream,
                                        "edl_gather_keys");
 }
 
-extern "C" int edl_gather_ids(const float* slab, int dim, const int64_t* ids, int64_t n,
+extern "C" int edl_gather_ids(const float* slab, int dim, int64_t row_stride, const int64_t* ids, int64_t n,
                               const int64_t* field_base, int n_fields, float* out,
                               edl_stream_t stream) {
   EDL_REQUIRE(n == 0 || ids, EDL_EINVAL, "edl_gather_ids: ids is null");
@@ -335,12 +363,12 @@ extern "C" int edl_gather_ids(const float* slab, int dim, const int64_t* ids, in
     const uint64_t e = M * d - (1ull << 32);          // 1 <= e <= d
     if ((uint64_t)(n - 1) <= 0xffffffffull / e) {
       IdsRowFnFast fn{ids, field_base, (unsigned)M, (unsigned)n_fields};
-      return launch_gather<IdsRowFnFast, false>(slab, dim, fn, n, nullptr, nullptr, out, (cudaStream_t)stream,
+      return launch_gather<IdsRowFnFast, false>(slab, dim, row_stride, fn, n, nullptr, nullptr, out, (cudaStream_t)stream,
                                                 "edl_gather_ids");
     }
   }
   IdsRowFn fn{ids, field_base, n_fields};
-  return launch_gather<IdsRowFn, false>(slab, dim, fn, n, nullptr, nullptr, out, (cudaStream_t)stream,
+  return launch_gather<IdsRowFn, false>(slab, dim, row_stride, fn, n, nullptr, nullptr, out, (cudaStream_t)stream,
                                         "edl_gather_ids");
 }
 
@@ -348,7 +376,7 @@ extern "C" int edl_expand(const float* rows, int dim, const int32_t* index, int6
                           edl_stream_t stream) {
   EDL_REQUIRE(n == 0 || index, EDL_EINVAL, "edl_expand: index is null");
   IndexRowFn fn{index};
-  return launch_gather<IndexRowFn, false>(rows, dim, fn, n, nullptr, nullptr, out, (cudaStream_t)stream,
+  return launch_gather<IndexRowFn, false>(rows, dim, 0, fn, n, nullptr, nullptr, out, (cudaStream_t)stream,
                                           "edl_expand");
 }
 
@@ -391,8 +419,10 @@ extern "C" int edl_compose_index(const int32_t* index, const int32_t* map, int64
 }
 
 extern "C" int edl_scatter_rows(const float* rows, int dim, const int32_t* pos, int64_t n,
-                                const int32_t* n_dev, float* out, edl_stream_t stream) {
+                                const int32_t* n_dev, float* out, int64_t out_row_stride, edl_stream_t stream) {
   EDL_REQUIRE(dim > 0 && dim % 4 == 0, EDL_EINVAL, "edl_scatter_rows: dim=%d must be a positive multiple of 4", dim);
+  int OS4 = 0;
+  { int rc0 = edl_row_stride4("edl_scatter_rows", dim, out_row_stride, &OS4); if (rc0) return rc0; }
   EDL_REQUIRE(n >= 0, EDL_EINVAL, "edl_scatter_rows: n negative");
   if (n == 0) return EDL_OK;
   EDL_REQUIRE(rows && pos && out, EDL_EINVAL, "edl_scatter_rows: null pointer");
@@ -400,10 +430,10 @@ extern "C" int edl_scatter_rows(const float* rows, int dim, const int32_t* pos, 
   const int g = grid_for(n * D4, 1);
   cudaStream_t st = (cudaStream_t)stream;
   switch (D4) {
-#define EDL_CASE(W) case W: k_scatter_rows<W><<<g, kThreads, 0, st>>>((const float4*)rows, D4, pos, n, n_dev, (float4*)out); break;
+#define EDL_CASE(W) case W: k_scatter_rows<W><<<g, kThreads, 0, st>>>((const float4*)rows, D4, OS4, pos, n, n_dev, (float4*)out); break;
     EDL_CASE(4) EDL_CASE(8) EDL_CASE(16) EDL_CASE(32) EDL_CASE(64)
 #undef EDL_CASE
-    default: k_scatter_rows<0><<<g, kThreads, 0, st>>>((const float4*)rows, D4, pos, n, n_dev, (float4*)out);
+    default: k_scatter_rows<0><<<g, kThreads, 0, st>>>((const float4*)rows, D4, OS4, pos, n, n_dev, (float4*)out);
   }
   EDL_LAUNCH_CHECK("k_scatter_rows");
   return EDL_OK;

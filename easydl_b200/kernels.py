@@ -36,6 +36,26 @@ def _need(t: torch.Tensor, dtype, name: str):
     return t
 
 
+def _rows(t: torch.Tensor, name: str):
+    """A [rows, dim] fp32 table or slot array whose rows may lie apart (a column window of interleaved
+    records): -> row stride in floats for the C ABI."""
+    if not t.is_cuda:
+        raise _lib.EdlError(f"{name} must be a CUDA tensor (there is no CPU path)")
+    if t.dtype != torch.float32 or t.dim() != 2:
+        raise TypeError(f"{name} must be float32 [rows, dim], got {t.dtype} {tuple(t.shape)}")
+    if t.shape[0] > 1 and t.shape[1] > 1 and t.stride(1) != 1:
+        raise ValueError(f"{name}: the elements of a row must be contiguous")
+    return int(t.stride(0)) if t.shape[0] > 1 else int(t.shape[1])
+
+
+def _same_stride(slab, *slots):
+    rs = _rows(slab, "slab")
+    for k, sl in enumerate(slots):
+        if sl is not None and _rows(sl, f"slot{k}") != rs:
+            raise ValueError("slab and optimizer slots must share one row stride")
+    return rs
+
+
 def _ws(nbytes: int, device) -> torch.Tensor:
     return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
 
@@ -49,14 +69,19 @@ def key_bits_for(total_rows: int) -> int:
 def init_rows(slab: torch.Tensor, layout: torch.Tensor, seed: int, row_begin: int = 0,
               n_rows: Optional[int] = None):
     lib = _lib.load()
-    _need(slab, torch.float32, "slab")
+    rs = _rows(slab, "slab")
     n_rows = slab.shape[0] - row_begin if n_rows is None else n_rows
-    check(lib.edl_init_rows(_ptr(slab), slab.shape[1], _ptr(layout), row_begin, n_rows,
+    check(lib.edl_init_rows(_ptr(slab), slab.shape[1], rs, _ptr(layout), row_begin, n_rows,
                             C.c_uint64(seed & (2 ** 64 - 1)), _stream()), "edl_init_rows")
 
 
 def fill(t: torch.Tensor, value: float):
     lib = _lib.load()
+    if t.dim() == 2 and not t.is_contiguous():     # a slot inside interleaved records
+        rs = _rows(t, "t")
+        check(lib.edl_fill_rows_f32(_ptr(t), t.shape[1], rs, t.shape[0], C.c_float(value), _stream()),
+              "edl_fill_rows_f32")
+        return
     _need(t, torch.float32, "t")
     check(lib.edl_fill_f32(_ptr(t), t.numel(), C.c_float(value), _stream()), "edl_fill_f32")
 
@@ -148,12 +173,12 @@ def partition_mod(keys: torch.Tensor, layout: Optional[torch.Tensor], num_shards
 def gather_keys(slab: torch.Tensor, keys: torch.Tensor, layout: Optional[torch.Tensor] = None, *,
                 n_dev: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None):
     lib = _lib.load()
-    _need(slab, torch.float32, "slab")
+    rs = _rows(slab, "slab")
     _need(keys, torch.int64, "keys")
     n, dim = keys.numel(), slab.shape[1]
     if out is None:
         out = torch.empty((n, dim), dtype=torch.float32, device=slab.device)
-    check(lib.edl_gather_keys(_ptr(slab), dim, _ptr(keys), n, _ptr(n_dev), _ptr(layout), _ptr(out),
+    check(lib.edl_gather_keys(_ptr(slab), dim, rs, _ptr(keys), n, _ptr(n_dev), _ptr(layout), _ptr(out),
                               _stream()), "edl_gather_keys")
     return out
 
@@ -161,13 +186,13 @@ def gather_keys(slab: torch.Tensor, keys: torch.Tensor, layout: Optional[torch.T
 def gather_ids(slab: torch.Tensor, ids: torch.Tensor, field_base: Optional[torch.Tensor], *,
                out: Optional[torch.Tensor] = None):
     lib = _lib.load()
-    _need(slab, torch.float32, "slab")
+    rs = _rows(slab, "slab")
     _need(ids, torch.int64, "ids")
     n, dim = ids.numel(), slab.shape[1]
     if out is None:
         out = torch.empty((n, dim), dtype=torch.float32, device=slab.device)
     nf = 0 if field_base is None else field_base.numel()
-    check(lib.edl_gather_ids(_ptr(slab), dim, _ptr(ids), n, _ptr(field_base), nf, _ptr(out),
+    check(lib.edl_gather_ids(_ptr(slab), dim, rs, _ptr(ids), n, _ptr(field_base), nf, _ptr(out),
                              _stream()), "edl_gather_ids")
     return out
 
@@ -269,9 +294,8 @@ def scatter_rows(rows: torch.Tensor, pos: torch.Tensor, out: torch.Tensor, *,
     lib = _lib.load()
     _need(rows, torch.float32, "rows")
     _need(pos, torch.int32, "pos")
-    _need(out, torch.float32, "out")
     check(lib.edl_scatter_rows(_ptr(rows), rows.shape[1], _ptr(pos), pos.numel(), _ptr(n_dev),
-                               _ptr(out), _stream()), "edl_scatter_rows")
+                               _ptr(out), _rows(out, "out"), _stream()), "edl_scatter_rows")
     return out
 
 
@@ -314,8 +338,7 @@ def segreduce_update(slab: torch.Tensor, slot0: torch.Tensor, slot1: Optional[to
     """grad rows may be float32 (a worker's raw gradient) or float64 (exchanged partial sums).
     n_rows: bound on the number of gradient rows referenced (default: all rows of `grad`)."""
     lib = _lib.load()
-    _need(slab, torch.float32, "slab")
-    _need(slot0, torch.float32, "slot0")
+    rs = _same_stride(slab, slot0, slot1)
     if grad.dtype not in (torch.float32, torch.float64):
         raise TypeError("grad must be float32 or float64")
     _need(grad, grad.dtype, "grad")
@@ -327,7 +350,7 @@ def segreduce_update(slab: torch.Tensor, slot0: torch.Tensor, slot1: Optional[to
     need = lib.edl_segreduce_workspace_bytes(max_unique, n_rows, dim)
     if workspace is None or workspace.numel() < need:
         workspace = _ws(need, slab.device)
-    check(lib.edl_segreduce_update(_ptr(slab), _ptr(slot0), _ptr(slot1), dim, _ptr(uniq),
+    check(lib.edl_segreduce_update(_ptr(slab), _ptr(slot0), _ptr(slot1), dim, rs, _ptr(uniq),
                                    _ptr(order), _ptr(seg_offsets), _ptr(seg_first), _ptr(n_unique),
                                    max_unique, n_rows, _ptr(grad), int(grad.dtype == torch.float64), _ptr(layout),
                                    C.byref(opt), _ptr(touched), _ptr(workspace), workspace.numel(),
@@ -354,7 +377,7 @@ def export_shard(slab, slot0, slot1, touched, n_rows: int, layout, capacity: int
     o1 = torch.empty_like(rows) if slot1 is not None else None
     n_out = torch.empty(1, dtype=torch.int32, device=dev)
     ws = _ws(lib.edl_export_workspace_bytes(n_rows), dev)
-    check(lib.edl_export_shard(_ptr(slab), _ptr(slot0), _ptr(slot1), dim, _ptr(touched), n_rows,
+    check(lib.edl_export_shard(_ptr(slab), _ptr(slot0), _ptr(slot1), dim, _same_stride(slab, slot0, slot1), _ptr(touched), n_rows,
                                _ptr(layout), capacity, _ptr(keys), _ptr(rows), _ptr(o0), _ptr(o1),
                                _ptr(n_out), _ptr(ws), ws.numel(), _stream()), "edl_export_shard")
     return keys, rows, o0, o1, n_out
@@ -364,6 +387,6 @@ def import_shard(slab, slot0, slot1, touched, layout, keys, rows, slot0_in, slot
     lib = _lib.load()
     _need(keys, torch.int64, "keys")
     _need(rows, torch.float32, "rows")
-    check(lib.edl_import_shard(_ptr(slab), _ptr(slot0), _ptr(slot1), slab.shape[1], _ptr(touched),
+    check(lib.edl_import_shard(_ptr(slab), _ptr(slot0), _ptr(slot1), slab.shape[1], _same_stride(slab, slot0, slot1), _ptr(touched),
                                _ptr(layout), _ptr(keys), _ptr(rows), _ptr(slot0_in), _ptr(slot1_in),
                                keys.numel(), _stream()), "edl_import_shard")

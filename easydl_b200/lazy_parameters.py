@@ -39,10 +39,12 @@ class LazyShardParameters:
         self.step = 0
         self.max_rows = int(max_rows)
         self.layout_dev = self.layout.to_device(self.device)
-        # + 1: the spare row that absorbs writes after an overflow (reported by materialised())
-        self.slab = torch.empty((self.max_rows + 1, dim), dtype=torch.float32, device=self.device)
-        self.slots = [torch.empty((self.max_rows + 1, dim), dtype=torch.float32, device=self.device)
-                      for _ in range(opt.n_slots)]
+        # + 1: the spare row that absorbs writes after an overflow (reported by materialised()).
+        # One record [p | slot0 | slot1] per row, as in ShardParameters (one DRAM page per updated id).
+        self.records = torch.empty((self.max_rows + 1, dim * (1 + opt.n_slots)), dtype=torch.float32, device=self.device)
+        self.slab = self.records[:, :dim]
+        self.slots = [self.records[:, dim * (k + 1):dim * (k + 2)] for k in range(opt.n_slots)]
+        self.row_stride = dim * (1 + opt.n_slots)
         self.index_capacity = _pow2_at_least(2 * self.max_rows)
         lib = _lib.load()
         self.index = torch.empty(lib.edl_lazy_index_bytes(self.index_capacity), dtype=torch.uint8,
@@ -76,7 +78,7 @@ class LazyShardParameters:
         if out is None:
             out = torch.empty((n, self.dim), dtype=torch.float32, device=self.device)
         check(lib.edl_lazy_gather(self.index.data_ptr(), self.index_capacity, self.slab.data_ptr(), self.dim,
-                                  K._ptr(keys), n, K._ptr(n_dev), self.layout_dev.data_ptr(),
+                                  self.row_stride, K._ptr(keys), n, K._ptr(n_dev), self.layout_dev.data_ptr(),
                                   C.c_uint64(self.seed & (2 ** 64 - 1)), K._ptr(out), K._stream()),
               "edl_lazy_gather")
         return out
@@ -93,7 +95,8 @@ class LazyShardParameters:
             slots = torch.empty(max(n, 1), dtype=torch.int64, device=self.device)
         s1 = self.slots[1] if len(self.slots) > 1 else None
         check(lib.edl_lazy_insert(self.index.data_ptr(), self.index_capacity, self.slab.data_ptr(),
-                                  self.slots[0].data_ptr(), K._ptr(s1), self.dim, self.max_rows, K._ptr(keys), n,
+                                  self.slots[0].data_ptr(), K._ptr(s1), self.dim, self.row_stride, self.max_rows,
+                                  K._ptr(keys), n,
                                   K._ptr(n_dev), self.layout_dev.data_ptr(), C.c_uint64(self.seed & (2 ** 64 - 1)),
                                   C.c_float(self.opt.slot_init(0)), C.c_float(self.opt.slot_init(1)),
                                   slots.data_ptr(), K._stream()), "edl_lazy_insert")

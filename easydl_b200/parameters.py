@@ -41,7 +41,8 @@ class ShardRecords:
 
 class ShardParameters:
     def __init__(self, rows: Sequence[int], dim: int, opt: OptimizerSpec, num_shards: int = 1,
-                 shard: int = 0, seed: int = DEFAULT_SEED, device="cuda:0", init: bool = True):
+                 shard: int = 0, seed: int = DEFAULT_SEED, device="cuda:0", init: bool = True,
+                 interleaved: bool = True):
         if dim <= 0 or dim % 4:
             raise ValueError("dim must be a positive multiple of 4")
         self.layout = ShardLayout(rows, num_shards, shard)
@@ -52,9 +53,20 @@ class ShardParameters:
         self.step = 0                      # number of applied batches (Adam's t)
         n = max(self.layout.local_rows, 1)
         self.layout_dev = self.layout.to_device(self.device)
-        self.slab = torch.empty((n, dim), dtype=torch.float32, device=self.device)
-        self.slots = [torch.empty((n, dim), dtype=torch.float32, device=self.device)
-                      for _ in range(opt.n_slots)]
+        # interleaved (default): one record [p | slot0 | slot1] per row -- an update touches one DRAM page
+        # and one TLB entry per id instead of one per array (tools/rowbw_probe: 4.39 -> 5.55 TB/s for the
+        # update's access pattern).  slab / slots are column windows of the records; the kernels take the
+        # row stride.  interleaved=False: separate dense arrays.
+        self.interleaved = bool(interleaved)
+        if self.interleaved:
+            self.records = torch.empty((n, dim * (1 + opt.n_slots)), dtype=torch.float32, device=self.device)
+            self.slab = self.records[:, :dim]
+            self.slots = [self.records[:, dim * (k + 1):dim * (k + 2)] for k in range(opt.n_slots)]
+        else:
+            self.records = None
+            self.slab = torch.empty((n, dim), dtype=torch.float32, device=self.device)
+            self.slots = [torch.empty((n, dim), dtype=torch.float32, device=self.device)
+                          for _ in range(opt.n_slots)]
         self.touched = torch.zeros((n + 31) // 32 + 1, dtype=torch.int32, device=self.device)
         # the optimizer rate as a device scalar, for launch sequences that are captured once and
         # replayed (Adam's lr_t changes every step): stage_rate() copies rate(step) into it
@@ -150,3 +162,7 @@ class ShardParameters:
 
     def nbytes(self) -> int:
         return self.slab.numel() * 4 * (1 + len(self.slots)) + self.touched.numel() * 4
+
+    def state_tensors(self):
+        """[parameter rows, slot rows...] as dense copies (tests, digests)."""
+        return [self.slab.contiguous()] + [s.contiguous() for s in self.slots]

@@ -280,6 +280,8 @@ class SlotShardedStep:
         self.phase_d_prepare()
         self.phase_d_apply(bump_step)
 
+    rate_on_device = False     # set by GraphedSlotStep: the optimizer rate is read from params.lr_dev
+
     def phase_d_prepare(self):
         """Needs only the received keys (fence 1): compact, dedup, slot-space order."""
         b, g, uq2 = self.buf, self.gen, self.uq2
@@ -295,7 +297,7 @@ class SlotShardedStep:
         slotted = K.UniqueResult(uniq=uq2.uniq, inverse=None, counts=None, order=self.order2,
                                  seg_offsets=uq2.seg_offsets, n_unique=uq2.n_unique, n=uq2.n, seg_first=self.first2)
         self.params.apply_gradients(slotted, b.own_region(g, "grads"), uq2.n, self.ws_seg, n_rows=uq2.n,
-                                    bump_step=bump_step)
+                                    bump_step=bump_step, rate_on_device=self.rate_on_device)
         self.gen ^= 1
 
     # ------------------------------------------------------------------ drivers
@@ -329,6 +331,31 @@ class SlotShardedStep:
         self.update(ids, grad)
         return emb
 
+    PHASES = ("A_dedup_partition_send", "fence1", "B_owner_gather", "fence2", "C_expand", "C_reduce_send", "fence3",
+              "D_owner_dedup", "D_owner_update")
+
+    def run_timed(self, ids: torch.Tensor, grad: torch.Tensor):
+        """One step with the phases in a row on the current stream (no helper streams) and a CUDA event
+        after each: -> [(phase name, event before, event after)].  For bench.py's per-phase times; every
+        rank must call it in lock step (the fences pair up)."""
+        marks = [torch.cuda.Event(enable_timing=True)]
+        marks[0].record()
+
+        def mark():
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            marks.append(e)
+        self.phase_a(ids); mark()
+        self.buf.fence(); mark()
+        self.phase_b(False); mark()
+        self.buf.fence(); mark()
+        self.phase_c_expand(); mark()
+        self.phase_c_reduce(grad); mark()
+        self.buf.fence(); mark()
+        self.phase_d_prepare(); mark()
+        self.phase_d_apply(); mark()
+        return [(n, marks[i], marks[i + 1]) for i, n in enumerate(self.PHASES)]
+
     def check(self):
         """Synchronise and raise if a slot overflowed or a fence timed out since the last check."""
         torch.cuda.synchronize(self.device)
@@ -355,14 +382,12 @@ def run_virtual(steps: Sequence[SlotShardedStep], ids: Sequence[torch.Tensor], g
 
 
 class GraphedSlotStep:
-    """SlotShardedStep replayed from CUDA graphs for one fixed (ids, grad) buffer pair: one graph per
-    buffer generation, replayed alternately.  Adagrad only (Adam's rate is a by-value argument that
-    changes every step).  Every rank must construct and replay in lock step."""
+    """SlotShardedStep (or PipelinedSlotStep) replayed from CUDA graphs for one fixed (ids, grad) buffer
+    pair: one graph per buffer generation, replayed alternately.  The optimizer rate is read from the
+    device scalar params.lr_dev, refreshed before every replay (Adam's rate changes every step).
+    Every rank must construct and replay in lock step."""
 
     def __init__(self, step: SlotShardedStep, ids: torch.Tensor, grad: torch.Tensor):
-        from ._lib import EDL_OPT_ADAGRAD
-        if step.params.opt.kind != EDL_OPT_ADAGRAD:
-            raise ValueError("GraphedSlotStep supports Adagrad only")
         self.step, self.ids, self.grad = step, ids, grad
         cur = torch.cuda.current_stream()
         side = torch.cuda.Stream()
@@ -374,16 +399,24 @@ class GraphedSlotStep:
         torch.cuda.synchronize()
         host_step = step.params.step
         self.graphs = [None, None]
-        for _ in (0, 1):                     # in the order the generations come up next
-            gen = step.gen
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                step.run(ids, grad)
-            self.graphs[gen] = g
+        lanes = getattr(step, "lanes", [step])
+        for l in lanes:
+            l.rate_on_device = True
+        try:
+            for _ in (0, 1):                 # in the order the generations come up next
+                gen = step.gen
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    step.run(ids, grad)
+                self.graphs[gen] = g
+        finally:
+            for l in lanes:
+                l.rate_on_device = False
         step.params.step = host_step
 
     def run(self) -> torch.Tensor:
         st = self.step                        # the generation lives on the step: several graphed
+        st.params.stage_rate(st.params.step + 1)
         self.graphs[st.gen].replay()          # (ids, grad) pairs may share one step
         st.gen ^= 1
         st.params.step += 1

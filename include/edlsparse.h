@@ -20,7 +20,13 @@
  *     consumers take the device pointer plus a host upper bound, so a whole step can be
  *     enqueued without a host synchronisation;
  *   - rows are fp32, row-major, `dim` a multiple of 4 (16-byte rows at least), row
- *     pointers 16-byte aligned.
+ *     pointers 16-byte aligned;
+ *   - "row_stride" (floats; 0 = dim): the distance between consecutive rows of a table / slot
+ *     array.  A shard may keep the parameter row and the optimizer-slot rows of one id side by side
+ *     in one record [p | slot0 | slot1]: slab = records, slot0 = records + dim, slot1 = records +
+ *     2 dim, row_stride = (1 + n_slots) * dim.  An id's update then touches ONE DRAM page and one
+ *     TLB entry instead of one per array: measured 4.39 -> 5.55 TB/s for the update's access
+ *     pattern on B200 (tools/rowbw_probe), which is bound by row activations, not by bytes.
  *
  * Fused keys.  Table t has rows_t hash buckets; key(t, id) = key_base[t] + id with
  * key_base the exclusive prefix sum of rows_t.  A `layout` is a device int64 array
@@ -62,6 +68,7 @@ const char* edl_last_error_string(void);
  *   classify_side (EDL_CLASSIFY_SIDE, 1)  forked launch: the hot-id listing runs on the helper stream too
  *   seg_impl      (EDL_SEG_IMPL, 1)       main reduce kernel: 1 = k_seg_stream (cp.async ring), 0 = k_seg_direct
  *   stream_ctas   (EDL_STREAM_CTAS, 3)    k_seg_stream: persistent CTAs per SM (capped by shared memory)
+ *   stream_stages (EDL_STREAM_STAGES, 4)  k_seg_stream: ring slots in use, 2..4 (bytes in flight per warp)
  *   direct_batch  (EDL_DIRECT_BATCH, 2)   k_seg_direct: ids per lane group
  *   gather_impl   (EDL_GATHER_IMPL, 1)    gather kernels: 1 = next iteration's row index prefetched
  * Unknown names and out-of-range values return EDL_EINVAL. */
@@ -72,10 +79,12 @@ int edl_tuning_get(const char* name, int* value_out);
  * Fills slab rows [row_begin, row_begin + n_rows) of this shard's slab with the pure
  * function init(seed, t, id, c).  layout is REQUIRED here, also for S == 1: the table of a slab
  * row, and with it the id the initialiser hashes, is found through local_base. */
-int edl_init_rows(float* slab, int dim, const int64_t* layout, int64_t row_begin, int64_t n_rows,
+int edl_init_rows(float* slab, int dim, int64_t row_stride, const int64_t* layout, int64_t row_begin, int64_t n_rows,
                   uint64_t seed, edl_stream_t stream);
 /* value fill for optimizer slots (Adagrad init_accum, Adam zeros) */
 int edl_fill_f32(float* dst, int64_t n, float value, edl_stream_t stream);
+/* the same for `dim`-wide rows that lie row_stride floats apart (a slot inside interleaved records) */
+int edl_fill_rows_f32(float* dst, int dim, int64_t row_stride, int64_t n_rows, float value, edl_stream_t stream);
 
 /* ---- A1 dedup / unique (lineage deduplicate_indexed_slices, unique half) ---------------
  * keys[j] = ids[j] + field_base[j % n_fields] (field_base NULL: keys = ids).
@@ -144,9 +153,9 @@ int edl_partition_mod(const int64_t* keys, int64_t n, const int32_t* n_dev, cons
  *                   of a [B, F] id batch without a dedup).
  * edl_expand      : out[j] = rows[index[j]], int32 index (worker-side expand by `inverse`).
  * n_dev nullable as above. */
-int edl_gather_keys(const float* slab, int dim, const int64_t* keys, int64_t n, const int32_t* n_dev,
+int edl_gather_keys(const float* slab, int dim, int64_t row_stride, const int64_t* keys, int64_t n, const int32_t* n_dev,
                     const int64_t* layout, float* out, edl_stream_t stream);
-int edl_gather_ids(const float* slab, int dim, const int64_t* ids, int64_t n,
+int edl_gather_ids(const float* slab, int dim, int64_t row_stride, const int64_t* ids, int64_t n,
                    const int64_t* field_base, int n_fields, float* out, edl_stream_t stream);
 int edl_expand(const float* rows, int dim, const int32_t* index, int64_t n, float* out,
                edl_stream_t stream);
@@ -208,13 +217,21 @@ typedef struct edl_opt_params {
                         * each replay (Adam's lr_t changes every step).  Zero the struct before filling it. */
 } edl_opt_params;
 
-int edl_segreduce_update(float* slab, float* slot0, float* slot1, int dim, const int64_t* uniq,
+int edl_segreduce_update(float* slab, float* slot0, float* slot1, int dim, int64_t row_stride, const int64_t* uniq,
                          const int32_t* order, const int32_t* seg_offsets,
                          const int32_t* seg_first /* nullable */, const int32_t* n_unique_dev,
                          int64_t max_unique, int64_t n_rows,
                          const void* grad, int grad_f64, const int64_t* layout, const edl_opt_params* opt_host,
                          uint32_t* touched, void* workspace, size_t workspace_bytes,
                          edl_stream_t stream);
+
+/* Self-test of the optimizer arithmetic (no lineage counterpart): the update kernels evaluate the IEEE
+ * square root and division of four row elements side by side with the hardware's own fast sequences
+ * and fall back to the generic routines outside their range.  This runs n pseudo-random operand
+ * triples -- half raw bit patterns (zeros, denormals, infinities, NaNs), half training-like magnitudes --
+ * through both forms, element-wise and composed as Adagrad / Adam steps, and ADDS the number of results
+ * that differ in any bit to *mismatches_dev (device uint64, zeroed by the caller).  Expected: 0. */
+int edl_selftest_rounding(int64_t n, uint64_t seed, uint64_t* mismatches_dev, edl_stream_t stream);
 
 /* ---- A6 elastic re-shard (lineage CheckpointSaver / restore_params_from_checkpoint) ----
  * edl_export_count : n_out (device int32) = number of set bits in touched[0..n_rows).
@@ -227,12 +244,12 @@ int edl_segreduce_update(float* slab, float* slot0, float* slot1, int dim, const
 size_t edl_export_workspace_bytes(int64_t n_rows);
 int edl_export_count(const uint32_t* touched, int64_t n_rows, int32_t* n_out, void* workspace,
                      size_t workspace_bytes, edl_stream_t stream);
-int edl_export_shard(const float* slab, const float* slot0, const float* slot1, int dim,
+int edl_export_shard(const float* slab, const float* slot0, const float* slot1, int dim, int64_t row_stride,
                      const uint32_t* touched, int64_t n_rows, const int64_t* layout,
                      int64_t capacity, int64_t* keys_out, float* rows_out, float* slot0_out,
                      float* slot1_out, int32_t* n_out, void* workspace, size_t workspace_bytes,
                      edl_stream_t stream);
-int edl_import_shard(float* slab, float* slot0, float* slot1, int dim, uint32_t* touched,
+int edl_import_shard(float* slab, float* slot0, float* slot1, int dim, int64_t row_stride, uint32_t* touched,
                      const int64_t* layout, const int64_t* keys, const float* rows,
                      const float* slot0_in, const float* slot1_in, int64_t n,
                      edl_stream_t stream);
@@ -240,7 +257,7 @@ int edl_import_shard(float* slab, float* slot0, float* slot1, int dim, uint32_t*
 /* ---- A7 exchange helpers: permute rows for the all-to-all-v send buffers --------------
  * out[i] = rows[perm[i]] is edl_expand.  Scatter form: out[pos[i]] = rows[i]. */
 int edl_scatter_rows(const float* rows, int dim, const int32_t* pos, int64_t n,
-                     const int32_t* n_dev, float* out, edl_stream_t stream);
+                     const int32_t* n_dev, float* out, int64_t out_row_stride /* floats; 0 = dim */, edl_stream_t stream);
 
 /* ---- lazily materialised rows (lineage EmbeddingTable.get lazy initialisation) --
  * For tables that do not fit densely (configs[2]: 1.6 TB with Adam state).  A shard stores only
@@ -258,11 +275,11 @@ int edl_scatter_rows(const float* rows, int dim, const int32_t* pos, int64_t n,
  *   edl_lazy_dump   : keys_out[s], slots_out[s] for every materialised row s (slot order). */
 size_t edl_lazy_index_bytes(int64_t index_capacity);
 int edl_lazy_clear(void* index, int64_t index_capacity, edl_stream_t stream);
-int edl_lazy_gather(const void* index, int64_t index_capacity, const float* slab, int dim,
+int edl_lazy_gather(const void* index, int64_t index_capacity, const float* slab, int dim, int64_t row_stride,
                     const int64_t* keys, int64_t n, const int32_t* n_dev, const int64_t* layout,
                     uint64_t seed, float* out, edl_stream_t stream);
 int edl_lazy_insert(void* index, int64_t index_capacity, float* slab, float* slot0, float* slot1,
-                    int dim, int64_t max_rows, const int64_t* keys, int64_t n, const int32_t* n_dev,
+                    int dim, int64_t row_stride, int64_t max_rows, const int64_t* keys, int64_t n, const int32_t* n_dev,
                     const int64_t* layout, uint64_t seed, float slot0_init, float slot1_init,
                     int64_t* slots_out, edl_stream_t stream);
 const int32_t* edl_lazy_status_ptr(const void* index, int64_t index_capacity);

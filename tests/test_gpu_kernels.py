@@ -359,13 +359,13 @@ def test_errors_are_reported_not_thrown(cuda):
         K.unique(torch.zeros(4, dtype=torch.int64), None, 8)
 
 
-def _three_steps_digest(dev, opt, dim=64, alpha=1.2):
+def _three_steps_digest(dev, opt, dim=64, alpha=1.2, interleaved=True):
     import hashlib
     from easydl_b200.criteo import CriteoSynthetic
     from easydl_b200.parameters import ShardParameters
     from easydl_b200.step import SparseStep
     rows = [50_000] * 26
-    P = ShardParameters(rows, dim, opt, device=dev)
+    P = ShardParameters(rows, dim, opt, device=dev, interleaved=interleaved)
     src = CriteoSynthetic(rows, 8192, alpha=alpha)
     st = SparseStep(P, 8192)
     h = hashlib.sha256()
@@ -389,15 +389,15 @@ def test_update_launch_variants_agree(cuda, opt_name, dim):
     plain one.  The knobs are switched in-process (edl_tuning_set)."""
     from easydl_b200 import _lib
     from easydl_b200.optimizer import OptimizerSpec
-    knobs = ("seg_impl", "seg_fork", "classify_side", "long_thr", "stream_ctas", "direct_batch", "gather_impl")
+    knobs = ("seg_impl", "seg_fork", "classify_side", "long_thr", "stream_ctas", "stream_stages", "direct_batch", "gather_impl")
     saved = {k: _lib.tuning_get(k) for k in knobs}
     variants = [
         dict(),                                               # defaults
         dict(seg_impl=0, gather_impl=0),                      # round-1 kernels
         dict(seg_impl=0, seg_fork=0, direct_batch=1),
         dict(seg_impl=1, seg_fork=0),
-        dict(seg_impl=1, classify_side=0, long_thr=4, stream_ctas=1),
-        dict(seg_impl=1, long_thr=100, stream_ctas=2),
+        dict(seg_impl=1, classify_side=0, long_thr=4, stream_ctas=1, stream_stages=2),
+        dict(seg_impl=1, long_thr=100, stream_ctas=2, stream_stages=3),
         dict(seg_impl=0, long_thr=3),
     ]
     opt = OptimizerSpec.adagrad() if opt_name == "adagrad" else OptimizerSpec.adam()
@@ -407,6 +407,10 @@ def test_update_launch_variants_agree(cuda, opt_name, dim):
             for k in knobs:
                 _lib.tuning_set(k, v.get(k, saved[k]))
             digests.append(_three_steps_digest(cuda, opt, dim))
+        for v in (dict(seg_impl=0), dict(seg_impl=1)):        # separate dense arrays instead of [p | slots] records
+            for k in knobs:
+                _lib.tuning_set(k, v.get(k, saved[k]))
+            digests.append(_three_steps_digest(cuda, opt, dim, interleaved=False))
     finally:
         for k in knobs:
             _lib.tuning_set(k, saved[k])
@@ -437,3 +441,16 @@ def test_c_host_program(cuda, tmp_path):
     r = subprocess.run([exe], capture_output=True, text=True, env=env, timeout=120)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "mismatching elements: 0" in r.stdout
+
+
+def test_four_wide_sqrt_div_are_ieee_exact(cuda):
+    """The update kernels' side-by-side sqrt / divide sequences against __fsqrt_rn / __fdiv_rn on 2^27
+    random operand triples (raw bit patterns and training-like magnitudes), element-wise and composed as
+    Adagrad / Adam steps: not one differing bit."""
+    from easydl_b200 import _lib
+    lib = _lib.load()
+    bad = torch.zeros(1, dtype=torch.int64, device=cuda)
+    for seed in (1, 0xDEADBEEF):
+        _lib.check(lib.edl_selftest_rounding(1 << 26, seed, bad.data_ptr(), torch.cuda.current_stream().cuda_stream),
+                   "edl_selftest_rounding")
+    assert int(bad.item()) == 0

@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     assert lib.edl_version() >= 100
     # argument errors come back as codes + message, without touching the GPU
     assert lib.edl_unique_workspace_bytes(1000, 28, 0, 0) > 0
-    rc = lib.edl_gather_keys(None, 6, None, 4, None, None, None, None)
+    rc = lib.edl_gather_keys(None, 6, 0, None, 4, None, None, None, None)
     assert rc == -1 and b"keys is null" in lib.edl_last_error_string()
 
 

@@ -27,7 +27,7 @@ DEFAULT_SETS = (
     "seg_impl=1,stream_ctas=3,long_thr=16,classify_side=0;"
     "seg_impl=1,stream_ctas=3,long_thr=16,seg_fork=0"
 )
-KNOBS = ("long_thr", "seg_fork", "classify_side", "seg_impl", "stream_ctas", "direct_batch", "gather_impl")
+KNOBS = ("long_thr", "seg_fork", "classify_side", "seg_impl", "stream_ctas", "stream_stages", "direct_batch", "gather_impl")
 
 
 def apply(setting, defaults):
@@ -65,6 +65,7 @@ def main():
     ap.add_argument("--n-batches", type=int, default=4)
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "knob_sweep.json"))
     ap.add_argument("--set", default=DEFAULT_SETS)
+    ap.add_argument("--dense-arrays", action="store_true", help="separate parameter / slot arrays instead of records")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)
@@ -83,7 +84,7 @@ def main():
     N = B * F
     rows = [a.rows] * F
     opt = OptimizerSpec.adagrad() if a.optimizer == "adagrad" else OptimizerSpec.adam()
-    P = ShardParameters(rows, D, opt, device=dev)
+    P = ShardParameters(rows, D, opt, device=dev, interleaved=not a.dense_arrays)
     step = SparseStep(P, B)
     src = CriteoSynthetic(rows, B, a.alpha)
     ids = [torch.from_numpy(src.ids(i)).to(dev) for i in range(a.n_batches)]
