@@ -61,10 +61,12 @@ def parse_args():
                          "IPC, fused with the producing kernels); nccl = all-to-all-v by NCCL; auto = slots "
                          "(measured fastest at 2 and 8 GPUs)")
     ap.add_argument("--lanes", type=int, default=2, help="--exchange slots-pipe: number of table groups")
-    ap.add_argument("--wire", default="f64", choices=["f64", "f32"],
-                    help="element type of exchanged partial gradient sums (N>1).  f64 is the parity-validated "
-                         "default; f32 halves the gradient bytes but breaks the 1e-6 tolerance for very hot ids "
-                         "(8 workers, tests/test_gpu_sharded.py) and for Adam")
+    ap.add_argument("--wire", default="auto", choices=["auto", "mixed", "f64", "f32"],
+                    help="exchanged partial gradient sums (N>1).  mixed (default with the slot exchanges): an id with "
+                         "one local gradient row travels as that fp32 row, the others as float64 partial sums -- bit "
+                         "for bit the result of the all-float64 wire at ~60 %% of its bytes; f64: all float64 "
+                         "(default of the peer / nccl exchanges); f32 halves the bytes but breaks the 1e-6 tolerance "
+                         "for very hot ids and for Adam")
     return ap.parse_args()
 
 
@@ -83,6 +85,14 @@ def algorithmic_bytes(N, U, D, optimizer):
     return lookup, update
 
 
+def _single_share(step):
+    """Share of this rank's unique ids (last step) that have exactly one gradient row (device scalar)."""
+    import torch
+    u = int(step.uq.n_unique.item())
+    seg = step.uq.seg_offsets[:u + 1]
+    return ((seg[1:] - seg[:-1]) == 1).sum().to(torch.float64) / max(u, 1)
+
+
 NVLINK_GBS = 770.0   # measured peer copy per direction per GPU on this pool (B200_PROFILING.md); nominal 900
 
 
@@ -91,8 +101,8 @@ def sharded_roofline(a, world, N, U, owner_counts, ms_step, peak, peak_kind):
     hit: bytes that must leave the GPU over NVLink, and bytes that must cross its own HBM.  frac = the
     larger of the two ideal times / the measured step time."""
     D, S = a.dim, world
-    wire = 8 if a.wire == "f64" else 4
-    R, Uo = owner_counts            # keys received per owner, unique among them
+    R, Uo, single_frac = owner_counts            # keys received per owner, unique among them, share of one-row ids
+    wire = {"f64": 8.0, "f32": 4.0, "mixed": 4.0 * single_frac + 8.0 * (1.0 - single_frac)}[a.wire]
     out_frac = (S - 1) / S
     nv = out_frac * (8 * U + 4 * D * R + wire * D * U)
     hbm = (8 * N                                   # A: ids (the sort's working set stays in L2)
@@ -111,7 +121,8 @@ def sharded_roofline(a, world, N, U, owner_counts, ms_step, peak, peak_kind):
             "nvlink_out_bytes_per_rank": nv, "hbm_bytes_per_rank": hbm,
             "ideal_nvlink_ms": t_nv * 1e3, "ideal_hbm_ms": t_hbm * 1e3,
             "nvlink_peak_note": "770 GB/s = measured peer copy per direction per GPU (B200_PROFILING.md); nominal 900",
-            "keys_received_per_owner": R, "unique_keys_per_owner": Uo}
+            "keys_received_per_owner": R, "unique_keys_per_owner": Uo,
+            "gradient_wire_bytes_per_element": wire, "single_row_id_share": single_frac}
 
 
 def measured_peak_gbs():
@@ -276,13 +287,18 @@ def run_b200_arm(a):
     N = B * F
     if a.exchange == "auto":
         a.exchange = "slots" if world > 1 else "peer"
+    if a.wire == "auto":
+        a.wire = "mixed" if (world > 1 and a.exchange in ("slots", "slots-pipe")) else "f64"
+    if a.wire == "mixed" and not (world > 1 and a.exchange in ("slots", "slots-pipe")):
+        raise SystemExit("--wire mixed is implemented by the slot exchanges (N > 1)")
+    wire_dtype = {"f64": torch.float64, "f32": torch.float32, "mixed": "mixed"}[a.wire]
 
     # ---------------- real-rank parity against the oracle, before anything is timed (N > 1)
     parity = None
     if world > 1 and not a.no_parity:
         from tools.parity import check_exchange
-        parity = check_exchange(a.exchange, dev, dist.group.WORLD,
-                                torch.float64 if a.wire == "f64" else torch.float32, a.lanes)
+        parity = check_exchange(a.exchange, dev, dist.group.WORLD, wire_dtype, a.lanes)
+        parity["wire"] = a.wire
         if not parity["ok"]:
             if rank == 0:
                 print(json.dumps({"metric": METRIC, "error": "parity check against the oracle failed",
@@ -299,7 +315,6 @@ def run_b200_arm(a):
     else:
         from easydl_b200.sharded_step import ShardedSparseStep
         from easydl_b200.exchange import PeerExchange, SingleExchange, TorchExchange
-        wire_dtype = torch.float64 if a.wire == "f64" else torch.float32
         slots = world > 1 and a.exchange in ("slots", "slots-pipe")
         if slots:
             ex = None
@@ -441,15 +456,17 @@ def run_b200_arm(a):
         t_ph = torch.tensor([acc[n] / k_ph for n in step.PHASES], dtype=torch.float64, device=dev)
         dist.all_reduce(t_ph, op=dist.ReduceOp.MAX)
         sharded_phases = {n + "_ms": float(t_ph[j].item()) for j, n in enumerate(step.PHASES)}
-        oc = torch.stack([step.n_recv[0].to(torch.float64), step.uq2.n_unique[0].to(torch.float64)])
+        oc = torch.stack([step.n_recv[0].to(torch.float64), step.uq2.n_unique[0].to(torch.float64),
+                          _single_share(step).to(torch.float64)])
         dist.all_reduce(oc, op=dist.ReduceOp.SUM)
-        owner_counts = (float(oc[0].item()) / world, float(oc[1].item()) / world)   # received keys, owner-unique keys
+        owner_counts = tuple(float(x) / world for x in oc.tolist())   # received keys, owner-unique keys, one-row share
     elif sharded and world > 1 and a.exchange == "slots-pipe":
         torch.cuda.synchronize()
         oc = torch.stack([sum(l.n_recv[0].to(torch.float64) for l in step.lanes),
-                          sum(l.uq2.n_unique[0].to(torch.float64) for l in step.lanes)])
+                          sum(l.uq2.n_unique[0].to(torch.float64) for l in step.lanes),
+                          sum(_single_share(l) for l in step.lanes).to(torch.float64) / len(step.lanes)])
         dist.all_reduce(oc, op=dist.ReduceOp.SUM)
-        owner_counts = (float(oc[0].item()) / world, float(oc[1].item()) / world)
+        owner_counts = tuple(float(x) / world for x in oc.tolist())
 
     # ---------------- end-to-end through the host-buffer PS API
     e2e = None

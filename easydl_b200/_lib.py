@@ -50,7 +50,7 @@ PROTOTYPES = {
     "edl_compose_index": (_int, [_p, _p, _i64, _p, _p]),
     "edl_segreduce_workspace_bytes": (_sz, [_i64, _i64, _int]),
     "edl_segreduce": (_int, [_p, _int, _p, _p, _p, _p, _i64, _i64, _p, _p, _int, _p, _p, _sz, _p]),
-    "edl_segreduce_update": (_int, [_p, _p, _p, _int, _i64, _p, _p, _p, _p, _p, _i64, _i64, _p, _int, _p,
+    "edl_segreduce_update": (_int, [_p, _p, _p, _int, _i64, _p, _p, _p, _p, _p, _i64, _i64, _p, _int, _p, _p,
                                     C.POINTER(OptParams), _p, _p, _sz, _p]),
     "edl_selftest_rounding": (_int, [_i64, C.c_uint64, _p, _p]),
     "edl_export_workspace_bytes": (_sz, [_i64]),
@@ -73,7 +73,7 @@ PROTOTYPES = {
     "edl_peer_copy": (_int, [_p, _p, _sz, _p]),
     "edl_peer_signal_wait": (_int, [_p, _p, _int, _int, _i64, _p]),
     "edl_peer_signal_wait_counter": (_int, [_p, _p, _int, _int, _p, _p]),
-    "edl_slot_send": (_int, [_p, _int, _p, _int, _p, _i64, _p, _p, _i64, _p]),
+    "edl_slot_send": (_int, [_p, _int, _p, _int, _p, _i64, _p, _p, _i64, _p, _p, _p]),
     "edl_slot_positions": (_int, [_p, _i64, _p, _p, _int, _i64, _p, _p]),
     "edl_slot_compact": (_int, [_p, _p, _int, _i64, _i64, _p, _p, _p, _p]),
     "edl_remap_index": (_int, [_p, _p, _i64, _p, _p, _p]),

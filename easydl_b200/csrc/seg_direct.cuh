@@ -19,7 +19,8 @@ constexpr int kUnrollC = 2;    // same, chunk path
 template <int kG, int kC, typename GT, typename Epi, int kMinBlocks = 4, int kUnroll = kUnrollD, int kMode = 0, int kBlock = kThreads,
           int kBatch = 1>
 __global__ void __launch_bounds__(kBlock, kMinBlocks)
-k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __restrict__ order,
+k_seg_direct(const unsigned char* __restrict__ grad, const unsigned char* __restrict__ grad32, int D4,
+             const int32_t* __restrict__ order,
              const int32_t* __restrict__ seg, const int32_t* __restrict__ seg_first,
              const int32_t* __restrict__ n_unique,
              const int64_t* __restrict__ uniq, const int64_t* __restrict__ layout, Epi epi,
@@ -32,7 +33,6 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
   epi.prepare();
   const int U = *n_unique;
   const int gl = threadIdx.x % kG;
-  const unsigned ROWB_G = (unsigned)D4 * R::kBytes4;
   // Each lane group takes kBatch ids, one CTA-width of groups apart.  The index loads (segment
   // bounds, first row, key) of ALL of them are issued before the first id's rows are touched, so the
   // first memory hop of ids 2..kBatch is hidden behind the work on the id before.
@@ -83,6 +83,7 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
     return;
   }
   const long long row = epi.row_from(&L, tok);
+  if (row < 0) return;   // a write epilogue dropped the row (beyond its slot)
   float4 p[kC], a0[kC], a1[kC];
 #pragma unroll
   for (int c = 0; c < kC; ++c) {
@@ -90,15 +91,19 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
     if (col < D4) epi.load(row, D4, col, &p[c], &a0[c], &a1[c]);   // in flight during the reduce
   }
   if (kMode != 2 && cnt == 1) {
-    const long long j = j0 >= 0 ? j0 : order[s0];
+    const int j = j0 >= 0 ? j0 : order[s0];
 #pragma unroll
     for (int c = 0; c < kC; ++c) {
       const int col = gl + c * kG;
       if (col < D4) {
-        typename R::V v = R::ldg(grad + (size_t)j * ROWB_G, col);
-        double s[4] = {0.0, 0.0, 0.0, 0.0};
-        if (Epi::kOutF64) R::add(s, v);
-        epi.apply(row, D4, col, R::f32(v), s, p[c], a0[c], a1[c]);
+        typename R::V v = R::row(grad, grad32, j, D4, col);
+        if constexpr (Epi::kMixed) {
+          epi.apply_single(row, D4, col, R::f32(v));   // one gradient row: it travels as it is
+        } else {
+          double s[4] = {0.0, 0.0, 0.0, 0.0};
+          if (Epi::kOutF64) R::add(s, v);
+          epi.apply(row, D4, col, R::f32(v), s, p[c], a0[c], a1[c]);
+        }
       }
     }
   } else if (kMode != 1) {
@@ -110,11 +115,11 @@ k_seg_direct(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
 #pragma unroll
       for (int k = 0; k < kUnroll; ++k) {
         if (i + k < s1) {
-          const long long j = order[i + k];
+          const int j = order[i + k];
 #pragma unroll
           for (int c = 0; c < kC; ++c) {
             const int col = gl + c * kG;
-            if (col < D4) v[k][c] = R::ldg(grad + (size_t)j * ROWB_G, col);
+            if (col < D4) v[k][c] = R::row(grad, grad32, j, D4, col);
           }
         }
       }
@@ -198,7 +203,8 @@ inline int fork_res(ForkRes** out) {
 // occupancy target by row width: 32 registers only pay off while one float4 per lane is live
 template <int kG, int kC, typename GT, typename Epi>
 __global__ void __launch_bounds__(kThreads, (kC == 1 ? 8 : (kC == 2 ? 4 : 2)))
-k_seg_chunk(const unsigned char* __restrict__ grad, int D4, const int32_t* __restrict__ order,
+k_seg_chunk(const unsigned char* __restrict__ grad, const unsigned char* __restrict__ grad32, int D4,
+            const int32_t* __restrict__ order,
             const int32_t* __restrict__ seg, const int32_t* __restrict__ counters,
             const int32_t* __restrict__ chunk_list, const int32_t* __restrict__ long_list,
             double* __restrict__ partial, const int64_t* __restrict__ uniq,
@@ -213,7 +219,6 @@ k_seg_chunk(const unsigned char* __restrict__ grad, int D4, const int32_t* __res
   const unsigned lane = threadIdx.x & 31u;
   const unsigned gmask = kG == 32 ? 0xffffffffu : (((1u << kG) - 1u) << (lane / kG * kG));
   const int groups = (int)((int64_t)gridDim.x * kThreads / kG);
-  const unsigned ROWB_G = (unsigned)D4 * R::kBytes4;
   const int D = D4 * 4;
   for (int ci = (int)(((int64_t)blockIdx.x * kThreads + threadIdx.x) / kG); ci < n_chunks; ci += groups) {
     const int4 ent = ((const int4*)chunk_list)[ci];
@@ -228,11 +233,11 @@ k_seg_chunk(const unsigned char* __restrict__ grad, int D4, const int32_t* __res
 #pragma unroll
       for (int k = 0; k < kUnrollC; ++k) {
         if (i + k < e) {
-          const long long j = order[i + k];
+          const int j = order[i + k];
 #pragma unroll
           for (int c = 0; c < kC; ++c) {
             const int col = gl + c * kG;
-            if (col < D4) v[k][c] = R::ldg(grad + (size_t)j * ROWB_G, col);
+            if (col < D4) v[k][c] = R::row(grad, grad32, j, D4, col);
           }
         }
       }
@@ -260,6 +265,7 @@ k_seg_chunk(const unsigned char* __restrict__ grad, int D4, const int32_t* __res
       continue;   // k_seg_long_final adds the partial rows of this id in chunk order
     }
     const long long row = epi.row_of(&L, uniq, u);
+    if (row < 0) continue;
 #pragma unroll
     for (int c = 0; c < kC; ++c) {
       const int col = gl + c * kG;
@@ -294,6 +300,7 @@ k_seg_long_final(int D4, const int32_t* __restrict__ counters, const int32_t* __
     const int u = le.x, base = le.w, nch = le.z;   // base: first partial row
     if (nch <= 1) continue;   // finished inside k_seg_chunk
     const long long row = epi.row_of(&L, uniq, u);
+    if (row < 0) continue;
     float4 p[kC], a0[kC], a1[kC];
     double acc[kC][4];
 #pragma unroll
@@ -349,7 +356,7 @@ k_seg_long_final(int D4, const int32_t* __restrict__ counters, const int32_t* __
 // seg_fork 1 (default): the hot-id branch runs on the device's helper stream beside the main kernel
 // (classify_side 1: from k_seg_classify on, so nothing precedes the main kernel on `st`).
 template <int kG, int kC, typename GT, typename Epi>
-int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t* seg,
+int launch_direct(const void* grad, const void* grad32, int D4, const int32_t* order, const int32_t* seg,
                   const int32_t* seg_first, const int32_t* n_unique, int64_t max_unique, const int64_t* uniq,
                   const int64_t* layout, Epi epi, const DirectWs& W, cudaStream_t st) {
   const int64_t ctas = edl_cdiv(max_unique * kG, kThreads);
@@ -375,7 +382,7 @@ int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t*
   };
   auto launch_hot = [&]() {
     const int64_t gc = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_chunks * kG, kThreads), EDL_SM_COUNT * 8));
-    k_seg_chunk<kG, kC, GT, Epi><<<(unsigned)gc, kThreads, 0, st_hot>>>((const unsigned char*)grad, D4, order, seg,
+    k_seg_chunk<kG, kC, GT, Epi><<<(unsigned)gc, kThreads, 0, st_hot>>>((const unsigned char*)grad, (const unsigned char*)grad32, D4, order, seg,
                                                                         W.counters, W.chunk_list, W.long_list, W.partial,
                                                                         uniq, layout, epi);
     const int64_t gf = std::max<int64_t>(1, std::min<int64_t>(edl_cdiv(W.max_long / 4 * kG, kThreads), EDL_SM_COUNT * 2));
@@ -392,12 +399,12 @@ int launch_direct(const void* grad, int D4, const int32_t* order, const int32_t*
     launch_classify(st);
   }
   if (impl == 1) {
-    int rc = launch_stream_main<kG, kC, GT, Epi>(grad, D4, order, seg, seg_first, n_unique, max_unique, uniq, layout,
+    int rc = launch_stream_main<kG, kC, GT, Epi>(grad, grad32, D4, order, seg, seg_first, n_unique, max_unique, uniq, layout,
                                                  epi, W.counters + 2, long_thr, st);
     if (rc) return rc;
   } else {
     int32_t* reg_counters = classify ? nullptr : W.counters;
-#define EDL_DARGS (const unsigned char*)grad, D4, order, seg, seg_first, n_unique, uniq, layout, epi, reg_counters, W.long_list, W.chunk_list, long_thr
+#define EDL_DARGS (const unsigned char*)grad, (const unsigned char*)grad32, D4, order, seg, seg_first, n_unique, uniq, layout, epi, reg_counters, W.long_list, W.chunk_list, long_thr
     if constexpr (kC == 1) {
       if (batch == 2)
         k_seg_direct<kG, kC, GT, Epi, 8, 1, 0, kThreads, 2><<<(unsigned)edl_cdiv(ctas, 2), kThreads, 0, st>>>(EDL_DARGS);
@@ -425,7 +432,7 @@ inline int seg_run_direct(const SegCall& c, const DirectWs& W) {
     using Epi = decltype(epi);
     return seg_with_dim(c.dim, [&](auto G, auto C) {
       return launch_direct<decltype(G)::value, decltype(C)::value, GT, Epi>(
-          c.grad, c.dim / 4, c.order, c.seg, c.seg_first, c.n_unique, c.max_unique, c.uniq, c.layout, epi, W, c.st);
+          c.grad, c.grad32, c.dim / 4, c.order, c.seg, c.seg_first, c.n_unique, c.max_unique, c.uniq, c.layout, epi, W, c.st);
     });
   });
 }

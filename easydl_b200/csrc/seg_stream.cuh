@@ -19,6 +19,7 @@
 // Summation order inside an id is its row order whatever the schedule: results are deterministic.
 #pragma once
 #include <atomic>
+#include <type_traits>
 
 #include "seg_common.cuh"
 
@@ -65,7 +66,8 @@ __device__ __forceinline__ void sts_u64(uint32_t a, unsigned long long v) {
 
 template <int kG, int kC, typename GT, typename Epi>
 __global__ void __launch_bounds__(kThreads, (StreamShape<kG, kC, GT, Epi>::kMinCtas))
-k_seg_stream(const unsigned char* __restrict__ grad, int D4, const int32_t* __restrict__ order,
+k_seg_stream(const unsigned char* __restrict__ grad, const unsigned char* __restrict__ grad32, int D4,
+             const int32_t* __restrict__ order,
              const int32_t* __restrict__ seg, const int32_t* __restrict__ seg_first,
              const int32_t* __restrict__ n_unique, const int64_t* __restrict__ uniq,
              const int64_t* __restrict__ layout, Epi epi, int32_t* __restrict__ ticket_counter, int kLongThr,
@@ -78,6 +80,7 @@ k_seg_stream(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
   epi.prepare();
   __syncthreads();
   constexpr unsigned kFull = 0xffffffffu;
+  constexpr bool kIsMixed = std::is_same<GT, MixedRow>::value;
   constexpr int kNS = S::kNS, kNP = S::kNP, kSlotP = S::kSlotP, kH = S::kH;
   constexpr uint32_t kStage = S::kStageBytes;
   const int U = *n_unique;
@@ -197,13 +200,22 @@ k_seg_stream(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
     unsigned long long d = 0;
     if (pos < end) {
       const bool last = pos + 1 == end;
-      const unsigned char* gsrc = grad + (size_t)j * ROWB_G + (size_t)gl * R::kBytes4;
+      bool narrow = false;   // mixed rows: this one is an fp32 row of grad32 (one piece per column)
+      if constexpr (kIsMixed) narrow = (j & kMixed32) != 0;
+      if (narrow) {
+        const unsigned char* gsrc = grad32 + (size_t)(j & (kMixed32 - 1)) * ((size_t)D4 * 16) + (size_t)gl * 16;
 #pragma unroll
-      for (int c = 0; c < kC; ++c) {
-        if (colok[c]) {
+        for (int c = 0; c < kC; ++c)
+          if (colok[c]) cp_async16_s(pbase + so_i + (kSlotP + c * kH) * 512u, gsrc + (size_t)c * kG * 16);
+      } else {
+        const unsigned char* gsrc = grad + (size_t)j * ROWB_G + (size_t)gl * R::kBytes4;
 #pragma unroll
-          for (int h = 0; h < kH; ++h)
-            cp_async16_s(pbase + so_i + (kSlotP + c * kH + h) * 512u, gsrc + (size_t)c * kG * R::kBytes4 + h * 16);
+        for (int c = 0; c < kC; ++c) {
+          if (colok[c]) {
+#pragma unroll
+            for (int h = 0; h < kH; ++h)
+              cp_async16_s(pbase + so_i + (kSlotP + c * kH + h) * 512u, gsrc + (size_t)c * kG * R::kBytes4 + h * 16);
+          }
         }
       }
       if (Epi::kSlots > 0 && last) {
@@ -216,7 +228,7 @@ k_seg_stream(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
             if (colok[c]) cp_async16_s(pbase + so_i + (s * kC + c) * 512u, b + (size_t)c * kG * 16);
         }
       }
-      d = 1ull | (fresh ? 2ull : 0ull) | (last ? 4ull : 0ull) | ((unsigned long long)row << 8);   // row < 2^40
+      d = 1ull | (fresh ? 2ull : 0ull) | (last ? 4ull : 0ull) | (narrow ? 8ull : 0ull) | ((unsigned long long)row << 8);   // row < 2^40
       fresh = false;
       ++pos;
       if (pos < end) j = __ldg(order + pos);   // needed one iteration from now
@@ -242,8 +254,12 @@ k_seg_stream(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
           if constexpr (kH == 1) {
             v[c] = lds_f4(cb + (kSlotP + c) * 512u);
           } else {
-            v[c].a = lds_d2(cb + (kSlotP + c * 2) * 512u);
-            v[c].b = lds_d2(cb + (kSlotP + c * 2 + 1) * 512u);
+            if (kIsMixed && (cd & 8ull)) {
+              if constexpr (kIsMixed) v[c] = R::widen(lds_f4(cb + (kSlotP + c * 2) * 512u));
+            } else {
+              v[c].a = lds_d2(cb + (kSlotP + c * 2) * 512u);
+              v[c].b = lds_d2(cb + (kSlotP + c * 2 + 1) * 512u);
+            }
           }
         }
       }
@@ -273,7 +289,8 @@ k_seg_stream(const unsigned char* __restrict__ grad, int D4, const int32_t* __re
             if (!first)
               g = make_float4(__double2float_rn(acc[c][0]), __double2float_rn(acc[c][1]),
                               __double2float_rn(acc[c][2]), __double2float_rn(acc[c][3]));
-            epi.apply(crow, D4, gl + c * kG, g, acc[c], p, a0, a1);
+            if (Epi::kMixed && first) epi.apply_single(crow, D4, gl + c * kG, g);   // one gradient row: sent as it is
+            else epi.apply(crow, D4, gl + c * kG, g, acc[c], p, a0, a1);
           }
         }
         if (gl == 0) epi.touch(crow);
@@ -303,7 +320,7 @@ int stream_attr_once(Kernel kernel, int smem_bytes, std::atomic<unsigned long lo
 // with lane groups half as wide and two float4 per lane: twice the ids per warp iteration, so the
 // per-iteration bookkeeping (hand-out shuffles, descriptors, address arithmetic) is paid half as often.
 template <int kG0, int kC0, typename GT, typename Epi>
-int launch_stream_main(const void* grad, int D4, const int32_t* order, const int32_t* seg, const int32_t* seg_first,
+int launch_stream_main(const void* grad, const void* grad32, int D4, const int32_t* order, const int32_t* seg, const int32_t* seg_first,
                        const int32_t* n_unique, int64_t max_unique, const int64_t* uniq, const int64_t* layout,
                        Epi epi, int32_t* ticket_counter, int long_thr, cudaStream_t st) {
   constexpr int kG = (kC0 == 1 && kG0 >= 8) ? kG0 / 2 : kG0;
@@ -316,7 +333,7 @@ int launch_stream_main(const void* grad, int D4, const int32_t* order, const int
   const int per_sm = std::max(1, std::min(edl_tune(EDL_TUNE_STREAM_CTAS), fit));
   const int64_t want = edl_cdiv(edl_cdiv(max_unique, 32), S::kWarps);
   const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(want, (int64_t)EDL_SM_COUNT * per_sm));
-  k_seg_stream<kG, kC, GT, Epi><<<grid, kThreads, S::kSmem, st>>>((const unsigned char*)grad, D4, order, seg, seg_first,
+  k_seg_stream<kG, kC, GT, Epi><<<grid, kThreads, S::kSmem, st>>>((const unsigned char*)grad, (const unsigned char*)grad32, D4, order, seg, seg_first,
                                                                   n_unique, uniq, layout, epi, ticket_counter, long_thr,
                                                                   edl_tune(EDL_TUNE_STREAM_STAGES));
   return EDL_OK;

@@ -25,7 +25,8 @@ __device__ __forceinline__ int slot_of(const int* __restrict__ offs, int S, int 
 __global__ void __launch_bounds__(kT)
 k_slot_send(const unsigned long long* __restrict__ rows, int words, const int32_t* __restrict__ offsets, int S,
             const long long* __restrict__ dst_bases, long long slot_limit,
-            const long long* __restrict__ count_ptrs, int32_t* __restrict__ err) {
+            const long long* __restrict__ count_ptrs, int32_t* __restrict__ err,
+            const int32_t* __restrict__ flag_seg, const int32_t* __restrict__ flag_perm) {
   __shared__ int offs[kMaxSlots + 1];
   for (int i = threadIdx.x; i <= S; i += kT) offs[i] = offsets[i];
   __syncthreads();
@@ -41,7 +42,12 @@ k_slot_send(const unsigned long long* __restrict__ rows, int words, const int32_
     const int d = slot_of(offs, S, p);
     const int k = p - offs[d];
     if (k >= slot_limit) continue;
-    ((unsigned long long*)dst_bases[d])[(long long)k * words + w] = rows[i];
+    unsigned long long v = rows[i];
+    if (flag_seg) {   // keys (one word per row): bit 62 marks an id with exactly one local gradient row
+      const int u = flag_perm[p];
+      if (flag_seg[u + 1] - flag_seg[u] == 1) v |= 1ull << 62;
+    }
+    ((unsigned long long*)dst_bases[d])[(long long)k * words + w] = v;
   }
 }
 
@@ -56,7 +62,9 @@ k_slot_positions(const int32_t* __restrict__ pos, long long n_max, const int32_t
   for (long long u = (long long)blockIdx.x * kT + threadIdx.x; u < n; u += (long long)gridDim.x * kT) {
     const int p = pos[u];
     const int d = slot_of(offs, S, p);
-    out[u] = (int32_t)((long long)d * slot_stride + (p - offs[d]));
+    long long k = p - offs[d];
+    if (k >= slot_stride) k = slot_stride - 1;   // a cut group (flagged by the sender): stay inside the slot
+    out[u] = (int32_t)((long long)d * slot_stride + k);
   }
 }
 
@@ -82,8 +90,9 @@ k_slot_compact(const long long* __restrict__ keys_slots, const int32_t* __restri
   for (long long i = (long long)blockIdx.x * kT + threadIdx.x; i < total; i += (long long)gridDim.x * kT) {
     const int s = slot_of(start, S, (int)i);
     const long long src = (long long)s * slot_stride + (i - start[s]);
-    keys_out[i] = keys_slots[src];
-    map_out[i] = (int32_t)src;
+    const long long k = keys_slots[src];
+    keys_out[i] = k & ~(1ll << 62);
+    map_out[i] = (int32_t)src | (((k >> 62) & 1) ? (1 << 30) : 0);   // bit 30: the gradient row is an fp32 row
   }
 }
 
@@ -127,7 +136,8 @@ inline unsigned grid_for(long long items) {
 
 extern "C" int edl_slot_send(const void* rows, int row_bytes, const int32_t* offsets_dev, int num_slots,
                              const int64_t* dst_bases_dev, int64_t slot_limit, const int64_t* count_ptrs_dev,
-                             int32_t* err_dev, int64_t n_max, edl_stream_t stream) {
+                             int32_t* err_dev, int64_t n_max, const int32_t* flag_seg_offsets, const int32_t* flag_perm,
+                             edl_stream_t stream) {
   EDL_REQUIRE(num_slots >= 1 && num_slots <= kMaxSlots, EDL_EINVAL, "edl_slot_send: num_slots=%d out of [1, %d]",
               num_slots, kMaxSlots);
   EDL_REQUIRE(row_bytes > 0 && row_bytes % 8 == 0, EDL_EINVAL, "edl_slot_send: row_bytes=%d must be a positive multiple of 8", row_bytes);
@@ -135,9 +145,11 @@ extern "C" int edl_slot_send(const void* rows, int row_bytes, const int32_t* off
   EDL_REQUIRE(n_max >= 0 && slot_limit >= 0, EDL_EINVAL, "edl_slot_send: negative size");
   EDL_REQUIRE(rows || n_max == 0, EDL_EINVAL, "edl_slot_send: rows is null");
   EDL_REQUIRE((((uintptr_t)rows) & 7) == 0, EDL_EINVAL, "edl_slot_send: rows must be 8-byte aligned");
+  EDL_REQUIRE(!flag_seg_offsets || (flag_perm && row_bytes == 8), EDL_EINVAL,
+              "edl_slot_send: the single-row flag applies to 8-byte keys and needs flag_perm");
   k_slot_send<<<grid_for(n_max * (row_bytes / 8)), kT, 0, (cudaStream_t)stream>>>(
       (const unsigned long long*)rows, row_bytes / 8, offsets_dev, num_slots, (const long long*)dst_bases_dev,
-      (long long)slot_limit, (const long long*)count_ptrs_dev, err_dev);
+      (long long)slot_limit, (const long long*)count_ptrs_dev, err_dev, flag_seg_offsets, flag_perm);
   EDL_LAUNCH_CHECK("k_slot_send");
   return EDL_OK;
 }
@@ -161,8 +173,8 @@ extern "C" int edl_slot_compact(const int64_t* keys_slots, const int32_t* counts
   EDL_REQUIRE(num_slots >= 1 && num_slots <= kMaxSlots, EDL_EINVAL, "edl_slot_compact: num_slots=%d out of range", num_slots);
   EDL_REQUIRE(keys_slots && counts_dev && keys_out && map_out && n_out_dev, EDL_EINVAL, "edl_slot_compact: null pointer");
   EDL_REQUIRE(slot_stride > 0 && slot_limit >= 0 && slot_limit <= slot_stride, EDL_EINVAL, "edl_slot_compact: bad slot sizes");
-  EDL_REQUIRE(slot_stride * num_slots < (int64_t)0x7fffffff && slot_limit * num_slots < (int64_t)0x7fffffff, EDL_ELIMIT,
-              "edl_slot_compact: slots do not fit an int32 row index");
+  EDL_REQUIRE(slot_stride * num_slots < (int64_t)(1 << 30) && slot_limit * num_slots < (int64_t)(1 << 30), EDL_ELIMIT,
+              "edl_slot_compact: slots do not fit a 30-bit row index");
   k_slot_compact<<<grid_for(slot_limit * num_slots), kT, 0, (cudaStream_t)stream>>>(
       (const long long*)keys_slots, counts_dev, num_slots, (long long)slot_stride, (long long)slot_limit,
       (long long*)keys_out, map_out, n_out_dev);

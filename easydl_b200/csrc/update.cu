@@ -75,10 +75,12 @@ extern "C" int edl_segreduce(const float* grad, int dim, const int32_t* order,
   EDL_REQUIRE(dst_table || (g_out && (((uintptr_t)g_out) & 15) == 0), EDL_EINVAL,
               "edl_segreduce: g_out null or misaligned (and no dst_table)");
   EDL_REQUIRE(!dst_table || out_pos, EDL_EINVAL, "edl_segreduce: dst_table needs out_pos");
+  EDL_REQUIRE(out_f64 >= 0 && out_f64 <= 2, EDL_EINVAL, "edl_segreduce: out_f64=%d not 0 (fp32), 1 (float64) or 2 (mixed)", out_f64);
+  EDL_REQUIRE(out_f64 != 2 || dst_table, EDL_EINVAL, "edl_segreduce: the mixed wire (out_f64 = 2) needs a dst_table");
   SegCall c{};
   c.grad = grad; c.dim = dim; c.grad_f64 = 0; c.order = order; c.seg = seg_offsets; c.seg_first = seg_first;
   c.n_unique = n_unique_dev; c.max_unique = max_unique; c.uniq = nullptr; c.layout = nullptr;
-  c.epi_kind = out_f64 ? 1 : 0; c.g_out = g_out; c.out_pos = out_pos; c.dst_table = dst_table;
+  c.epi_kind = out_f64 == 2 ? 4 : (out_f64 ? 1 : 0); c.g_out = g_out; c.out_pos = out_pos; c.dst_table = dst_table;
   c.st = (cudaStream_t)stream;
   return run_call(c, W);
 }
@@ -88,7 +90,7 @@ extern "C" int edl_segreduce_update(float* slab, float* slot0, float* slot1, int
                                     const int32_t* seg_offsets, const int32_t* seg_first,
                                     const int32_t* n_unique_dev,
                                     int64_t max_unique, int64_t n_rows, const void* grad, int grad_f64,
-                                    const int64_t* layout, const edl_opt_params* opt,
+                                    const float* grad32, const int64_t* layout, const edl_opt_params* opt,
                                     uint32_t* touched, void* workspace, size_t workspace_bytes,
                                     edl_stream_t stream) {
   if (max_unique == 0) return EDL_OK;
@@ -111,7 +113,10 @@ extern "C" int edl_segreduce_update(float* slab, float* slot0, float* slot1, int
               "edl_segreduce_update: unknown optimizer kind %d", opt->kind);
   EDL_REQUIRE(opt->kind != EDL_OPT_ADAM || slot1, EDL_EINVAL, "edl_segreduce_update: Adam needs slot1 (v)");
   SegCall c{};
-  c.grad = grad; c.dim = dim; c.grad_f64 = grad_f64; c.order = order; c.seg = seg_offsets; c.seg_first = seg_first;
+  EDL_REQUIRE(grad_f64 >= 0 && grad_f64 <= 2, EDL_EINVAL, "edl_segreduce_update: grad_f64=%d not 0, 1 or 2", grad_f64);
+  EDL_REQUIRE(grad_f64 != 2 || (grad32 && (((uintptr_t)grad32) & 15) == 0), EDL_EINVAL,
+              "edl_segreduce_update: mixed gradient rows (grad_f64 = 2) need grad32");
+  c.grad = grad; c.grad32 = grad32; c.dim = dim; c.grad_f64 = grad_f64; c.order = order; c.seg = seg_offsets; c.seg_first = seg_first;
   c.n_unique = n_unique_dev; c.max_unique = max_unique; c.uniq = uniq; c.layout = layout;
   c.epi_kind = opt->kind == EDL_OPT_ADAGRAD ? 2 : 3;
   c.slab = slab; c.slot0 = slot0; c.slot1 = slot1; c.touched = touched; c.opt = o; c.rs4 = RS4;

@@ -289,7 +289,7 @@ class PeerExchange:
         M = self.M if direction == "fwd" else self.M.t()
         roff = self.region_off[(self.gen, tag)]
         bases = [self.base[d] + roff + int(M[:self.rank, d].sum()) * rb for d in range(self.world)]
-        t = [self.world] + [int(x) for x in offsets] + bases
+        t = [self.world, 0] + [int(x) for x in offsets] + bases + [0] * self.world   # no slot limit, no fp32 region
         return torch.tensor(t, dtype=torch.int64, device=self.device)
 
     def finish_round(self, tag: str, recv):

@@ -237,8 +237,10 @@ def compose_index(index: torch.Tensor, mapping: torch.Tensor):
 
 # ------------------------------------------------------------------------------- A7 (slot rounds)
 def slot_send(rows: torch.Tensor, offsets: torch.Tensor, dst_bases: torch.Tensor, slot_limit: int,
-              count_ptrs: Optional[torch.Tensor], err: torch.Tensor, n_max: int):
-    """rows (partition order, any dtype with 8-byte-multiple rows) -> this rank's slot at every peer."""
+              count_ptrs: Optional[torch.Tensor], err: torch.Tensor, n_max: int,
+              flag_seg: Optional[torch.Tensor] = None, flag_perm: Optional[torch.Tensor] = None):
+    """rows (partition order, any dtype with 8-byte-multiple rows) -> this rank's slot at every peer.
+    flag_seg / flag_perm: mark the keys of ids with one local gradient row (bit 62; the narrow wire)."""
     lib = _lib.load()
     _need(offsets, torch.int32, "offsets")
     _need(dst_bases, torch.int64, "dst_bases")
@@ -247,7 +249,8 @@ def slot_send(rows: torch.Tensor, offsets: torch.Tensor, dst_bases: torch.Tensor
         raise ValueError("rows must be contiguous")
     row_bytes = rows.element_size() * (rows.numel() // max(rows.shape[0], 1)) if rows.dim() > 1 else rows.element_size()
     check(lib.edl_slot_send(_ptr(rows), row_bytes, _ptr(offsets), offsets.numel() - 1, _ptr(dst_bases),
-                            slot_limit, _ptr(count_ptrs), _ptr(err), n_max, _stream()), "edl_slot_send")
+                            slot_limit, _ptr(count_ptrs), _ptr(err), n_max, _ptr(flag_seg), _ptr(flag_perm),
+                            _stream()), "edl_slot_send")
 
 
 def slot_positions(pos: torch.Tensor, n_dev: Optional[torch.Tensor], offsets: torch.Tensor, slot_stride: int,
@@ -316,14 +319,18 @@ def segreduce(grad: torch.Tensor, order: torch.Tensor, seg_offsets: torch.Tensor
     if out is None and dst_table is None:
         out = torch.empty((max_unique, dim), dtype=out_dtype, device=grad.device)
     odt = out.dtype if out is not None else out_dtype
-    if odt not in (torch.float32, torch.float64):
-        raise TypeError("segreduce output must be float32 or float64")
+    mixed = odt == "mixed"
+    if not mixed and odt not in (torch.float32, torch.float64):
+        raise TypeError("segreduce output must be float32, float64 or 'mixed'")
+    if mixed and dst_table is None:
+        raise ValueError("the mixed wire needs a dst_table")
     n_rows = grad.shape[0]
     need = lib.edl_segreduce_workspace_bytes(max_unique, n_rows, dim)
     if workspace is None or workspace.numel() < need:
         workspace = _ws(need, grad.device)
     check(lib.edl_segreduce(_ptr(grad), dim, _ptr(order), _ptr(seg_offsets), _ptr(seg_first),
-                            _ptr(n_unique), max_unique, n_rows, _ptr(out_pos), _ptr(out), int(odt == torch.float64),
+                            _ptr(n_unique), max_unique, n_rows, _ptr(out_pos), _ptr(out),
+                            2 if mixed else int(odt == torch.float64),
                             _ptr(dst_table), _ptr(workspace), workspace.numel(), _stream()), "edl_segreduce")
     return out
 
@@ -334,9 +341,11 @@ def segreduce_update(slab: torch.Tensor, slot0: torch.Tensor, slot1: Optional[to
                      layout: Optional[torch.Tensor], opt: OptParams,
                      touched: Optional[torch.Tensor] = None,
                      workspace: Optional[torch.Tensor] = None,
-                     seg_first: Optional[torch.Tensor] = None, n_rows: Optional[int] = None):
-    """grad rows may be float32 (a worker's raw gradient) or float64 (exchanged partial sums).
-    n_rows: bound on the number of gradient rows referenced (default: all rows of `grad`)."""
+                     seg_first: Optional[torch.Tensor] = None, n_rows: Optional[int] = None,
+                     grad32: Optional[torch.Tensor] = None):
+    """grad rows may be float32 (a worker's raw gradient) or float64 (exchanged partial sums); with
+    grad32 given they are MIXED: row indices with bit 30 set name fp32 rows of grad32, the others float64
+    rows of grad.  n_rows: bound on the number of gradient rows referenced (default: all rows of `grad`)."""
     lib = _lib.load()
     rs = _same_stride(slab, slot0, slot1)
     if grad.dtype not in (torch.float32, torch.float64):
@@ -352,7 +361,8 @@ def segreduce_update(slab: torch.Tensor, slot0: torch.Tensor, slot1: Optional[to
         workspace = _ws(need, slab.device)
     check(lib.edl_segreduce_update(_ptr(slab), _ptr(slot0), _ptr(slot1), dim, rs, _ptr(uniq),
                                    _ptr(order), _ptr(seg_offsets), _ptr(seg_first), _ptr(n_unique),
-                                   max_unique, n_rows, _ptr(grad), int(grad.dtype == torch.float64), _ptr(layout),
+                                   max_unique, n_rows, _ptr(grad),
+                                   2 if grad32 is not None else int(grad.dtype == torch.float64), _ptr(grad32), _ptr(layout),
                                    C.byref(opt), _ptr(touched), _ptr(workspace), workspace.numel(),
                                    _stream()), "edl_segreduce_update")
 

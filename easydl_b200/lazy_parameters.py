@@ -114,7 +114,7 @@ class LazyShardParameters:
 
     def apply_gradients(self, uq: K.UniqueResult, grad: torch.Tensor, max_unique: Optional[int] = None,
                         workspace=None, n_rows: Optional[int] = None, bump_step: bool = True,
-                        rate_on_device: bool = False):
+                        rate_on_device: bool = False, grad32: Optional[torch.Tensor] = None):
         """Same signature as ShardParameters.apply_gradients: insert-if-absent for the unique keys, then the
         fused reduce + optimizer on their slab rows."""
         if bump_step:
@@ -124,7 +124,7 @@ class LazyShardParameters:
         opt = self.opt.params(self.step, self.lr_dev.data_ptr() if rate_on_device else 0)
         K.segreduce_update(self.slab, self.slots[0], s1, slots, uq.order, uq.seg_offsets, uq.n_unique,
                            uq.n if max_unique is None else max_unique, grad, None,
-                           opt, None, workspace, seg_first=uq.seg_first, n_rows=n_rows)
+                           opt, None, workspace, seg_first=uq.seg_first, n_rows=n_rows, grad32=grad32)
 
     # ------------------------------------------------------------------ A6
     def export_records(self) -> ShardRecords:

@@ -42,7 +42,7 @@ class ShardRecords:
 class ShardParameters:
     def __init__(self, rows: Sequence[int], dim: int, opt: OptimizerSpec, num_shards: int = 1,
                  shard: int = 0, seed: int = DEFAULT_SEED, device="cuda:0", init: bool = True,
-                 interleaved: bool = True):
+                 interleaved: bool = False):
         if dim <= 0 or dim % 4:
             raise ValueError("dim must be a positive multiple of 4")
         self.layout = ShardLayout(rows, num_shards, shard)
@@ -53,10 +53,12 @@ class ShardParameters:
         self.step = 0                      # number of applied batches (Adam's t)
         n = max(self.layout.local_rows, 1)
         self.layout_dev = self.layout.to_device(self.device)
-        # interleaved (default): one record [p | slot0 | slot1] per row -- an update touches one DRAM page
-        # and one TLB entry per id instead of one per array (tools/rowbw_probe: 4.39 -> 5.55 TB/s for the
-        # update's access pattern).  slab / slots are column windows of the records; the kernels take the
-        # row stride.  interleaved=False: separate dense arrays.
+        # interleaved: one record [p | slot0 | slot1] per row -- an update touches one DRAM page and one TLB
+        # entry per id instead of one per array; slab / slots are then column windows of the records and the
+        # kernels take the row stride.  Measured on B200 at cfg2 (profiles/r2_experiments.md): the bare access
+        # pattern gains 27 % (tools/rowbw_probe), the update kernels as they are gain nothing (they are bound
+        # by dependent-load latency, not by row activations) and the lookup loses 15 % (it reads every other
+        # 256-byte block), so separate dense arrays stay the default.
         self.interleaved = bool(interleaved)
         if self.interleaved:
             self.records = torch.empty((n, dim * (1 + opt.n_slots)), dtype=torch.float32, device=self.device)
@@ -116,7 +118,7 @@ class ShardParameters:
 
     def apply_gradients(self, uq: K.UniqueResult, grad: torch.Tensor, max_unique: Optional[int] = None,
                         workspace=None, n_rows: Optional[int] = None, bump_step: bool = True,
-                        rate_on_device: bool = False):
+                        rate_on_device: bool = False, grad32: Optional[torch.Tensor] = None):
         """Segment-sum grad rows per unique key and run the optimizer on the touched rows.
         bump_step=False: a further part of the same training step (disjoint ids), same step number.
         rate_on_device: the kernels read the rate from lr_dev (see stage_rate) instead of taking it by value."""
@@ -127,7 +129,7 @@ class ShardParameters:
         K.segreduce_update(self.slab, self.slots[0], slot1, uq.uniq, uq.order, uq.seg_offsets,
                            uq.n_unique, uq.n if max_unique is None else max_unique, grad,
                            self._layout_arg, opt, self.touched, workspace,
-                           seg_first=uq.seg_first, n_rows=n_rows)
+                           seg_first=uq.seg_first, n_rows=n_rows, grad32=grad32)
 
     # ------------------------------------------------------------------ A6
     def export_records(self) -> ShardRecords:

@@ -69,7 +69,7 @@ int main(void) {
   edl_opt_params opt;
   memset(&opt, 0, sizeof opt);
   opt.kind = EDL_OPT_ADAGRAD; opt.lr = 0.05f; opt.eps = 1e-7f;
-  CK(edl_segreduce_update(d_slab, d_acc, NULL, DIM, 0 /* dense rows */, d_uniq, d_order, d_seg, d_first, d_nu, N, N, d_grad, 0, NULL,
+  CK(edl_segreduce_update(d_slab, d_acc, NULL, DIM, 0 /* dense rows */, d_uniq, d_order, d_seg, d_first, d_nu, N, N, d_grad, 0, NULL, NULL,
                           &opt, NULL, ws_s, wss, NULL));
   CU(cudaDeviceSynchronize());
 

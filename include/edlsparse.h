@@ -173,13 +173,20 @@ int edl_compose_index(const int32_t* index, const int32_t* map, int64_t n, int32
  * g_out[dst(u)] = sum over i in [seg_offsets[u], seg_offsets[u+1]) of grad[order[i]],
  * accumulated in float64.  dst(u) = out_pos ? out_pos[u] : u.
  * out_f64 == 0: g_out is float[.., dim], the sum rounded once to fp32.
- * out_f64 != 0: g_out is double[.., dim], the float64 partial sums themselves -- the exact
+ * out_f64 == 1: g_out is double[.., dim], the float64 partial sums themselves -- the exact
  *               wire format of the worker -> PS gradient exchange (the owner's total is then
  *               independent of how the batch was split over workers, up to float64 rounding).
+ * out_f64 == 2: the exact NARROW wire (needs dst_table): an id with one gradient row is stored as that
+ *               fp32 row at base32[s] (its partial sum is an fp32 value), every other id as float64 at
+ *               base[s]; the receiver sums both kinds in float64 (edl_segreduce_update grad_f64 == 2),
+ *               bit for bit what the all-float64 wire gives, at ~60 % of its bytes on Zipf 1.05.
  * dst_table (nullable, needs out_pos): fused reduce -> send.  Device int64 array
- *   [ G, offsets[0..G], base[0..G-1] ]: output row dst(u) of group s (offsets[s] <= dst < offsets[s+1])
- *   is stored at address base[s] + (dst - offsets[s]) rows instead of in g_out; base[s] may be another
- *   GPU's memory mapped with edl_ipc_import, so the partial sums travel over NVLink as they are made.
+ *   [ G, slot_limit, offsets[0..G], base[0..G-1], base32[0..G-1] ]: output row dst(u) of group s
+ *   (offsets[s] <= dst < offsets[s+1]) is stored at address base[s] + (dst - offsets[s]) rows instead of
+ *   in g_out; base[s] may be another GPU's memory mapped with edl_ipc_import, so the partial sums travel
+ *   over NVLink as they are made.  slot_limit > 0: rows at or beyond it within their group are dropped
+ *   (the slot holds no more; the sender of the keys has flagged the overflow).  base32 is read by the
+ *   mixed wire only (pass zeros otherwise).
  * n_unique_dev: device int32 U; max_unique: host upper bound on U; n_rows: number of gradient
  * rows (= length of `order`), which bounds the scratch for hot ids.
  * Streams: edl_segreduce and edl_segreduce_update run the kernels for hot ids (more than 16
@@ -199,8 +206,10 @@ int edl_segreduce(const float* grad, int dim, const int32_t* order, const int32_
 
 /* ---- A4 + A5 fused: reduce, then optimizer row update in place (lineage PS
  * push_gradients -> optimizer kernel) -------------------------------------------------------
- * For each unique u: g = segment sum as above (grad rows are float, or double when
- * grad_f64 != 0), rounded once to fp32; row = row(uniq[u]) through layout;
+ * For each unique u: g = segment sum as above, rounded once to fp32; row = row(uniq[u]) through layout.
+ * Gradient rows: grad_f64 == 0: float rows in `grad`; 1: double rows in `grad` (exchanged partial sums);
+ * 2: MIXED -- a row index (order / seg_first entry) with bit 30 set names a float row of `grad32`, any
+ * other index a double row of `grad` (the exact narrow wire, see edl_segreduce out_f64 == 2).
  * Adagrad: acc += g*g; p -= lr*g/(sqrt(acc)+eps)                       (slot0 = acc)
  * Adam   : m = b1*m+(1-b1)*g; v = b2*v+((1-b2)*g)*g; p -= lr_t*m/(sqrt(v)+eps)
  *          (slot0 = m, slot1 = v; lr_t computed by the caller in float64, passed in `lr` or through `lr_dev`)
@@ -221,7 +230,7 @@ int edl_segreduce_update(float* slab, float* slot0, float* slot1, int dim, int64
                          const int32_t* order, const int32_t* seg_offsets,
                          const int32_t* seg_first /* nullable */, const int32_t* n_unique_dev,
                          int64_t max_unique, int64_t n_rows,
-                         const void* grad, int grad_f64, const int64_t* layout, const edl_opt_params* opt_host,
+                         const void* grad, int grad_f64, const float* grad32, const int64_t* layout, const edl_opt_params* opt_host,
                          uint32_t* touched, void* workspace, size_t workspace_bytes,
                          edl_stream_t stream);
 
@@ -323,15 +332,21 @@ int edl_peer_signal_wait_counter(const int64_t* peer_flag_ptrs_dev, int64_t* own
  *                    addresses of int32 cells that receive the group sizes.  Groups longer than
  *                    slot_limit are cut there and *err_dev |= 1 (check it after the step).
  *                    n_max: host bound on offsets[num_slots] (sizes the grid only).
- * edl_slot_positions: out[u] = d * slot_stride + (pos[u] - offsets[d]), the slot-space row of
- *                    partition position pos[u] (receiver side of the rows round).
+ *                    flag_seg_offsets / flag_perm (nullable; 8-byte keys only): row p is unique id
+ *                    u = flag_perm[p] of an edl_unique result with segment offsets flag_seg_offsets; keys
+ *                    of ids with exactly ONE gradient row are sent with bit 62 set (the narrow wire: the
+ *                    owner will find that id's partial sum as an fp32 row).
+ * edl_slot_positions: out[u] = d * slot_stride + min(pos[u] - offsets[d], slot_stride - 1), the
+ *                    slot-space row of partition position pos[u] (receiver side of the rows round).
  * edl_slot_compact : owner side: slots of keys with counts[s] valid rows -> contiguous keys_out in
- *                    slot (= peer rank) order, map_out[i] = slot-space row of keys_out[i], *n_out.
+ *                    slot (= peer rank) order with bit 62 cleared, map_out[i] = slot-space row of
+ *                    keys_out[i], with bit 30 set where the key carried bit 62, and *n_out.
  * edl_remap_index  : out[i] = map[index[i]] for i < *n_dev (edl_compose_index with a device count):
  *                    turns the `order` / `seg_first` of edl_unique(keys_out) into slot-space rows. */
 int edl_slot_send(const void* rows, int row_bytes, const int32_t* offsets_dev, int num_slots,
                   const int64_t* dst_bases_dev, int64_t slot_limit, const int64_t* count_ptrs_dev,
-                  int32_t* err_dev, int64_t n_max, edl_stream_t stream);
+                  int32_t* err_dev, int64_t n_max, const int32_t* flag_seg_offsets, const int32_t* flag_perm,
+                  edl_stream_t stream);
 int edl_slot_positions(const int32_t* pos, int64_t n_max, const int32_t* n_dev, const int32_t* offsets_dev,
                        int num_slots, int64_t slot_stride, int32_t* out, edl_stream_t stream);
 int edl_slot_compact(const int64_t* keys_slots, const int32_t* counts_dev, int num_slots, int64_t slot_stride,

@@ -80,25 +80,29 @@ def test_fence_with_device_counter_world_of_one(cuda):
     assert flags.cpu().tolist() == [3, 0] and int(counter.item()) == 3
 
 
-def _virtual(cuda, rows, dim, S, opt_name, batch, wire=torch.float64, slack=1.5):
+def _virtual(cuda, rows, dim, S, opt_name, batch, wire=torch.float64, slack=1.5, tight=True):
     from easydl_b200.optimizer import OptimizerSpec
     from easydl_b200.parameters import ShardParameters
     from easydl_b200.slot_step import SlotBuffers, SlotShardedStep
     po = OptimizerSpec.adagrad() if opt_name == "adagrad" else OptimizerSpec.adam()
     params = [ShardParameters(rows, dim, po, S, s, device=cuda) for s in range(S)]
-    bufs = [SlotBuffers(S, s, cuda, batch * len(rows), dim, wire) for s in range(S)]
+    N = batch * len(rows)
+    # tight: slots exactly as long as the step's slot limit (what a real rank allocates); else worst case
+    stride = min(N, int(slack * N / S) + 1024) if tight else N
+    bufs = [SlotBuffers(S, s, cuda, stride, dim, wire) for s in range(S)]
     for b in bufs:
         b.connect_local(bufs)
     steps = [SlotShardedStep(p, batch, b, wire_dtype=wire, slot_slack=slack) for p, b in zip(params, bufs)]
     return params, bufs, steps
 
 
-@pytest.mark.parametrize("S,opt", [(1, "adagrad"), (2, "adagrad"), (4, "adam"), (6, "adagrad"), (8, "adam")])
-def test_slot_step_matches_global_oracle(cuda, S, opt):
+@pytest.mark.parametrize("S,opt,wire", [(1, "adagrad", torch.float64), (2, "adagrad", "mixed"), (4, "adam", torch.float64),
+                                        (6, "adagrad", torch.float64), (8, "adam", "mixed"), (3, "adam", "mixed")])
+def test_slot_step_matches_global_oracle(cuda, S, opt, wire):
     from easydl_b200.slot_step import run_virtual
     from test_gpu_sharded import _compare_state, bits
     rows, dim, batch, steps = [5000, 301, 70001, 11, 6], 32, 512, 3
-    params, bufs, st = _virtual(cuda, rows, dim, S, opt, batch)
+    params, bufs, st = _virtual(cuda, rows, dim, S, opt, batch, wire=wire)
     oo = O.OptimizerSpec.adagrad() if opt == "adagrad" else O.OptimizerSpec.adam()
     osh = [O.OracleShard(rows, dim, oo, S, s) for s in range(S)]
     bases = O.key_bases(rows)
@@ -148,6 +152,33 @@ def test_slot_step_same_bits_as_packed_exchange(cuda):
         assert torch.equal(p.slab, q.slab) and torch.equal(p.slots[0], q.slots[0]) and p.step == q.step
     for b in bufs:
         b.close()
+
+
+def test_mixed_wire_gives_the_bits_of_the_float64_wire(cuda):
+    """fp32 rows for ids with one local gradient row + float64 partial sums for the rest: the owner's
+    float64 total, and with it every updated row and slot, is bit-identical to the all-float64 wire."""
+    from easydl_b200.slot_step import run_virtual
+    rows, dim, batch, S = [20000, 3000, 17, 500000], 64, 2048, 4
+    for opt in ("adagrad", "adam"):
+        pa, ba, sa = _virtual(cuda, rows, dim, S, opt, batch, wire=torch.float64, tight=False)
+        pb, bb, sb = _virtual(cuda, rows, dim, S, opt, batch, wire="mixed")
+        for k in range(3):
+            di, dg = [], []
+            for r in range(S):
+                _, ids, _ = O.criteo_batch(rows, batch, 1.1, step=k * 8 + r)
+                di.append(dev(ids, cuda)); dg.append(dev(O.synthetic_grad(ids.size, dim, step=k * 8 + r), cuda))
+            ea = run_virtual(sa, di, dg)
+            eb = run_virtual(sb, di, dg)
+            for x, y in zip(ea, eb):
+                assert torch.equal(x, y)
+        for s in sa + sb:
+            s.check()
+        for p, q in zip(pa, pb):
+            assert torch.equal(p.slab, q.slab) and p.step == q.step
+            for u, v in zip(p.slots, q.slots):
+                assert torch.equal(u, v)
+        for b in ba + bb:
+            b.close()
 
 
 def test_slot_overflow_is_reported(cuda):

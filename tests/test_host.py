@@ -132,7 +132,8 @@ def test_slot_buffer_layout_regions_do_not_overlap():
     counter and the overflow flag are disjoint, aligned, and sized for world x stride rows."""
     from easydl_b200.slot_step import slot_layout
     for world, stride, dim, wb in [(1, 7, 4, 8), (2, 1000, 64, 8), (8, 1703936, 64, 8), (6, 333, 128, 4)]:
-        offs, flags_off, counter_off, err_off, nbytes, rb = slot_layout(world, stride, dim, wb)
+        mixed = wb == 8 and world % 2 == 0
+        offs, flags_off, counter_off, err_off, nbytes, rb = slot_layout(world, stride, dim, wb, mixed)
         spans = []
         for (gen, region), o in offs.items():
             rows = world * stride if region != "counts" else world
@@ -145,7 +146,7 @@ def test_slot_buffer_layout_regions_do_not_overlap():
         for (a0, a1), (b0, b1) in zip(spans[:-1], spans[1:]):
             assert a1 <= b0
         assert spans[-1][1] <= nbytes
-        assert rb == {"keys": 8, "rows": dim * 4, "grads": dim * wb, "counts": 4}
+        assert rb == {"keys": 8, "rows": dim * 4, "grads": dim * wb, "grads32": dim * 4 if mixed else 0, "counts": 4}
         assert world * stride < 2 ** 31           # slot-space rows are int32
 
 

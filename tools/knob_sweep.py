@@ -65,7 +65,7 @@ def main():
     ap.add_argument("--n-batches", type=int, default=4)
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "knob_sweep.json"))
     ap.add_argument("--set", default=DEFAULT_SETS)
-    ap.add_argument("--dense-arrays", action="store_true", help="separate parameter / slot arrays instead of records")
+    ap.add_argument("--interleaved", action="store_true", help="[p | slots] records instead of separate dense arrays")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)
@@ -84,7 +84,7 @@ def main():
     N = B * F
     rows = [a.rows] * F
     opt = OptimizerSpec.adagrad() if a.optimizer == "adagrad" else OptimizerSpec.adam()
-    P = ShardParameters(rows, D, opt, device=dev, interleaved=not a.dense_arrays)
+    P = ShardParameters(rows, D, opt, device=dev, interleaved=a.interleaved)
     step = SparseStep(P, B)
     src = CriteoSynthetic(rows, B, a.alpha)
     ids = [torch.from_numpy(src.ids(i)).to(dev) for i in range(a.n_batches)]
