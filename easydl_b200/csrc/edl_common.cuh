@@ -8,6 +8,9 @@
 
 #define EDL_SM_COUNT 148          // B200: 2 dies x 74 SMs
 #define EDL_MAX_TABLES 64         // layout decode stages key_base/local_base in shared memory
+// Bit 62 of a fused key on the wire marks "this sender has exactly one gradient row for the id" (slot
+// exchange, narrow gradient wire).  Lookups by key ignore it; edl_slot_compact strips it.
+#define EDL_KEY_FLAG_SINGLE (1ll << 62)
 
 void edl_set_error(const char* fmt, ...);
 

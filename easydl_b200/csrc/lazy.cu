@@ -68,7 +68,7 @@ k_lazy_gather(const long long* __restrict__ idx_keys, const int* __restrict__ id
   for (int64_t e = (int64_t)blockIdx.x * kThreads + threadIdx.x; e < total; e += (int64_t)gridDim.x * kThreads) {
     const int64_t i = e / D4;
     const int c = (int)(e - i * D4);
-    const long long key = keys[i];
+    const long long key = keys[i] & ~EDL_KEY_FLAG_SINGLE;
     const long long slot = probe(idx_keys, idx_slot, mask, key);
     out[e] = slot >= 0 ? slab[slot * RS4 + c] : init_row4(&L, key, D4, c, seed);
   }

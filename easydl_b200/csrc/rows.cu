@@ -81,7 +81,7 @@ k_fill(float* __restrict__ dst, int64_t n, float value) {
 struct KeyRowFn {  // fused key -> slab row through the shard layout
   const int64_t* keys;
   __device__ __forceinline__ long long row(const EdlLayoutSmem* L, int64_t i) const {
-    return edl_key_to_row(L, keys[i]);
+    return edl_key_to_row(L, keys[i] & ~EDL_KEY_FLAG_SINGLE);
   }
 };
 struct IdsRowFn {  // raw ids[B, F] on one shard: slab row = id + field_base[f]

@@ -45,7 +45,7 @@ k_slot_send(const unsigned long long* __restrict__ rows, int words, const int32_
     unsigned long long v = rows[i];
     if (flag_seg) {   // keys (one word per row): bit 62 marks an id with exactly one local gradient row
       const int u = flag_perm[p];
-      if (flag_seg[u + 1] - flag_seg[u] == 1) v |= 1ull << 62;
+      if (flag_seg[u + 1] - flag_seg[u] == 1) v |= (unsigned long long)EDL_KEY_FLAG_SINGLE;
     }
     ((unsigned long long*)dst_bases[d])[(long long)k * words + w] = v;
   }
@@ -91,7 +91,7 @@ k_slot_compact(const long long* __restrict__ keys_slots, const int32_t* __restri
     const int s = slot_of(start, S, (int)i);
     const long long src = (long long)s * slot_stride + (i - start[s]);
     const long long k = keys_slots[src];
-    keys_out[i] = k & ~(1ll << 62);
+    keys_out[i] = k & ~EDL_KEY_FLAG_SINGLE;
     map_out[i] = (int32_t)src | (((k >> 62) & 1) ? (1 << 30) : 0);   // bit 30: the gradient row is an fp32 row
   }
 }

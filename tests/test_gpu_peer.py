@@ -38,7 +38,7 @@ def test_segreduce_dst_table_equals_plain_scatter(cuda, wire):
     bufs = [torch.zeros((offs[s + 1] - offs[s] + 5, dim), dtype=wire, device=cuda) for s in range(3)]
     shift = [2, 0, 5]                                   # rows of "lower ranks" already in each buffer
     esz = 8 if wire == torch.float64 else 4
-    table = [3] + offs + [bufs[s].data_ptr() + shift[s] * dim * esz for s in range(3)]
+    table = [3, 0] + offs + [bufs[s].data_ptr() + shift[s] * dim * esz for s in range(3)] + [0, 0, 0]
     K.segreduce(dev(grad, cuda), r.order, r.seg_offsets, r.n_unique, n, seg_first=r.seg_first,
                 out_pos=part.pos, out=None, out_dtype=wire,
                 dst_table=torch.tensor(table, dtype=torch.int64, device=cuda))
