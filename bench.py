@@ -53,6 +53,10 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="N>1: skip the oracle parity check before the warm-up")
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
+    ap.add_argument("--lazy-rows", type=int, default=0,
+                    help="N>1, slot exchanges: shards that store only updated rows (LazyShardParameters) with room for "
+                         "this many rows each -- for tables whose dense shards do not fit (BASELINE.json configs[2]: "
+                         "26 x 40M x dim 128 with Adam state is 200 GB per GPU on eight GPUs)")
     ap.add_argument("--force-sharded", action="store_true",
                     help="N=1 only: run the multi-shard code path (dedup/partition/exchange/expand) with S=1")
     ap.add_argument("--exchange", default="auto", choices=["auto", "peer", "nccl", "slots", "slots-pipe"],
@@ -222,7 +226,7 @@ def config_for(a, world, U_mean=None, sharded=False, nb=None):
     return {"workload": workload_name(a), "global_batch": B * world, "tables": F, "rows_per_table": a.rows,
             "dim": D, "zipf_alpha": a.alpha, "optimizer": a.optimizer, "unique_per_step": U_mean,
             "sharding": f"row-wise id mod {world}",
-            "code_path": "sharded" if sharded else "single-shard fused",
+            "code_path": ("sharded, lazily materialised rows" if getattr(a, "lazy_rows", 0) else "sharded") if sharded else "single-shard fused",
             "gradient_wire": a.wire if sharded else None,
             "exchange": (a.exchange if world > 1 else None),
             "cache": f"inputs larger than L2: {table_gb * (1 + slots):.0f} GB of table + optimizer rows touched at "
@@ -297,8 +301,14 @@ def run_b200_arm(a):
     parity = None
     if world > 1 and not a.no_parity:
         from tools.parity import check_exchange
-        parity = check_exchange(a.exchange, dev, dist.group.WORLD, wire_dtype, a.lanes)
+        factory = None
+        if a.lazy_rows:
+            from easydl_b200.lazy_parameters import LazyShardParameters
+            from tools.parity import ROWS as P_ROWS, DIM as P_DIM
+            factory = lambda po: LazyShardParameters(P_ROWS, P_DIM, po, world, rank, max_rows=1 << 17, device=dev)
+        parity = check_exchange(a.exchange, dev, dist.group.WORLD, wire_dtype, a.lanes, params_factory=factory)
         parity["wire"] = a.wire
+        parity["shards"] = "lazy" if a.lazy_rows else "dense"
         if not parity["ok"]:
             if rank == 0:
                 print(json.dumps({"metric": METRIC, "error": "parity check against the oracle failed",
@@ -306,7 +316,13 @@ def run_b200_arm(a):
             dist.destroy_process_group()
             raise SystemExit(3)
 
-    params = ShardParameters(rows, D, opt, world, rank, device=dev)
+    if a.lazy_rows:
+        if not (world > 1 and a.exchange in ("slots", "slots-pipe")):
+            raise SystemExit("--lazy-rows runs on the slot exchanges (N > 1)")
+        from easydl_b200.lazy_parameters import LazyShardParameters
+        params = LazyShardParameters(rows, D, opt, world, rank, max_rows=a.lazy_rows, device=dev)
+    else:
+        params = ShardParameters(rows, D, opt, world, rank, device=dev)
 
     sharded = world > 1 or a.force_sharded
     if not sharded:

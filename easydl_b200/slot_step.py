@@ -380,6 +380,8 @@ class SlotShardedStep:
                                "raise slot_slack")
         if late:
             raise RuntimeError("SlotShardedStep: a peer did not reach the exchange fence (timeout)")
+        if hasattr(self.params, "materialised"):
+            self.params.materialised()      # lazily materialised shard: raises if it ran out of rows
 
 
 def run_virtual(steps: Sequence[SlotShardedStep], ids: Sequence[torch.Tensor], grads: Sequence[torch.Tensor]):

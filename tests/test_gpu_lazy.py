@@ -116,3 +116,45 @@ def test_cfg3_full_id_space_8_shards_and_reshard(cuda):
         for i, k in enumerate(rec.keys.tolist()):
             assert np.array_equal(bits(rec.rows[i].numpy()), bits(before[k]))
     train(new, osh, 2, 1)
+
+
+@pytest.mark.parametrize("opt,wire", [("adam", "mixed"), ("adagrad", torch.float64)])
+def test_slot_step_on_lazy_shards(cuda, opt, wire):
+    """The host-sync-free slot step on lazily materialised shards (what configs[2] runs on real ranks):
+    4 virtual ranks, full 40M-row id space, against the oracle; then the slot-limit / row-limit check."""
+    from easydl_b200.lazy_parameters import LazyShardParameters
+    from easydl_b200.optimizer import OptimizerSpec
+    from easydl_b200.slot_step import SlotBuffers, SlotShardedStep, run_virtual
+    rows, dim, S, B = [40_000_000] * 6, 32, 4, 1024
+    po = OptimizerSpec.adam() if opt == "adam" else OptimizerSpec.adagrad()
+    oo = O.OptimizerSpec.adam() if opt == "adam" else O.OptimizerSpec.adagrad()
+    params = [LazyShardParameters(rows, dim, po, S, s, max_rows=1 << 15, device=cuda) for s in range(S)]
+    N = B * len(rows)
+    stride = min(N, int(1.5 * N / S) + 1024)
+    bufs = [SlotBuffers(S, s, cuda, stride, dim, wire) for s in range(S)]
+    for b in bufs:
+        b.connect_local(bufs)
+    st = [SlotShardedStep(p, B, b, wire_dtype=wire) for p, b in zip(params, bufs)]
+    osh = [O.OracleShard(rows, dim, oo, S, s) for s in range(S)]
+    bases = O.key_bases(rows)
+    for k in range(3):
+        kw, gw, di, dg = [], [], [], []
+        for r in range(S):
+            _, ids, _ = O.criteo_batch(rows, B, 1.05, step=k * 8 + r)
+            g = O.synthetic_grad(ids.size, dim, step=k * 8 + r)
+            kw.append(O.fuse_keys(ids, bases)); gw.append(g)
+            di.append(dev(ids, cuda)); dg.append(dev(g, cuda))
+        embs = run_virtual(st, di, dg)
+        want = O.sharded_step(osh, kw, gw)
+        for r in range(S):
+            _close(embs[r].cpu().numpy(), want[r], f"emb step {k} rank {r}")
+    for s in st:
+        s.check()
+    for p, o in zip(params, osh):
+        rec = p.export_records().cpu()
+        assert np.array_equal(rec.keys.numpy(), o.keys)
+        _close(rec.rows.numpy(), o.w, "rows")
+        for i in range(oo.n_slots):
+            _close(rec.slots[i].numpy(), o.slots[i], f"slot {i}")
+    for b in bufs:
+        b.close()

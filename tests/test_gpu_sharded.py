@@ -193,3 +193,43 @@ def test_checkpoint_reshard_files(cuda, opt, tmp_path):
                     assert np.array_equal(bits(rec.slots[kk][i].numpy()), bits(before[k][1][kk]))
             tot += len(rec)
         assert tot == len(before)
+
+
+@pytest.mark.parametrize("kind,opt", [("dense", "adagrad"), ("dense", "adam"), ("lazy", "adam")])
+def test_failed_ps_shard_recovers_from_its_checkpoint(cuda, tmp_path, kind, opt):
+    """ref:README.md:27 "recover failed parameter servers ... and resume the training": three PS shards
+    train, checkpoint at step 2, train on; shard 1 then dies (its device state is gone).  A fresh shard 1
+    restores from the newest COMPLETE version, the survivors roll back to the same version, training
+    resumes from there -- and the whole trajectory still matches the oracle, which took no failure."""
+    import copy
+    from easydl_b200 import checkpoint as ck
+    from easydl_b200.lazy_parameters import LazyShardParameters
+    from easydl_b200.optimizer import OptimizerSpec
+    from easydl_b200.parameters import ShardParameters
+    rows, dim, S, B = [5000, 301, 70001, 11, 6], 16, 3, 256
+    po = OptimizerSpec.adagrad() if opt == "adagrad" else OptimizerSpec.adam()
+    oo = O.OptimizerSpec.adagrad() if opt == "adagrad" else O.OptimizerSpec.adam()
+
+    def make(s):
+        if kind == "lazy":
+            return LazyShardParameters(rows, dim, po, S, s, max_rows=1 << 14, device=cuda)
+        return ShardParameters(rows, dim, po, S, s, device=cuda)
+    params = [make(s) for s in range(S)]
+    osh = [O.OracleShard(rows, dim, oo, S, s) for s in range(S)]
+    _train(cuda, params, osh, rows, dim, B, 2, 1.05, step0=0)
+    saver = ck.CheckpointSaver(str(tmp_path), keep_max=2)
+    for p in params:
+        saver.save(p)
+    osh_at_ckpt = copy.deepcopy(osh)
+    _train(cuda, params, osh, rows, dim, B, 1, 1.05, step0=2, fresh=False)          # progress that will be lost
+    # a version that only shard 0 managed to write before the failure: must be skipped by the restore
+    ck.write_shard_file(ck.shard_file(str(tmp_path), 3, 0, S), params[0].layout, dim, po.kind, params[0].export_records().cpu())
+    params[1] = None                                                                  # the PS Pod is gone
+    params[1] = make(1)
+    assert ck.latest_complete_version(str(tmp_path)) == 2
+    for p in params:
+        assert ck.restore_params_from_checkpoint(str(tmp_path), p) == 2
+    osh = osh_at_ckpt
+    _compare_state(cuda, params, osh, oo.n_slots)
+    _train(cuda, params, osh, rows, dim, B, 2, 1.05, step0=2, fresh=False)
+    _compare_state(cuda, params, osh, oo.n_slots)

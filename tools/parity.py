@@ -107,7 +107,7 @@ def check_exchange(kind: str, dev, group=None, wire_dtype=torch.float64, lanes: 
             ids_d, g_d = last
             states = []
             for replay in (False, True):
-                P2 = ShardParameters(ROWS, DIM, po, world, rank, device=dev)
+                P2 = params_factory(po) if params_factory else ShardParameters(ROWS, DIM, po, world, rank, device=dev)
                 st2, _ = _make_step(kind, P2, group, dev, wire_dtype, lanes)
                 if replay:
                     gs = GraphedSlotStep(st2, ids_d, g_d)      # two eager steps inside
@@ -117,11 +117,12 @@ def check_exchange(kind: str, dev, group=None, wire_dtype=torch.float64, lanes: 
                     for _ in range(4):
                         st2.run(ids_d, g_d)
                 st2.check()
-                states.append((P2.slab.clone(), [s.clone() for s in P2.slots], P2.step))
+                r2 = P2.export_records()     # dense and lazy shards alike: the materialised rows, ascending by key
+                states.append((r2.keys.clone(), r2.rows.clone(), [s.clone() for s in r2.slots], P2.step))
                 _close(st2, None)
                 del st2, P2
-            same = torch.equal(states[0][0], states[1][0]) and states[0][2] == states[1][2] and \
-                all(torch.equal(a, b) for a, b in zip(states[0][1], states[1][1]))
+            same = torch.equal(states[0][0], states[1][0]) and torch.equal(states[0][1], states[1][1]) and \
+                states[0][3] == states[1][3] and all(torch.equal(a, b) for a, b in zip(states[0][2], states[1][2]))
             graph_equal = same if graph_equal is None else (graph_equal and same)
             ok &= same
     flag = torch.tensor([1 if ok else 0], device=dev)
