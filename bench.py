@@ -51,6 +51,8 @@ def parse_args():
     ap.add_argument("--cpu-steps", type=int, default=3, help="timed oracle steps for cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-prefetch", action="store_true",
+                    help="N=1: time only the strictly sequential step (no dedup of the next batch beside the update)")
     ap.add_argument("--no-parity", action="store_true", help="N>1: skip the oracle parity check before the warm-up")
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying CUDA graphs")
     ap.add_argument("--lazy-rows", type=int, default=0,
@@ -370,6 +372,14 @@ def run_b200_arm(a):
     # ---------------- device-resident timed region
     # S == 1, Adagrad: the step is replayed from CUDA graphs (one per id batch buffer), which
     # removes the host launch gaps between its 17 kernels.  Otherwise: eager launches.
+    # unique ids per batch (deterministic per batch buffer): read once, outside the timed region
+    U_batch = []
+    for i in range(nb):
+        if not sharded:
+            U_batch.append(int(step.dedup(ids_dev[i]).n_unique.item()))
+        else:
+            step.run(ids_dev[i], grad_dev)
+            U_batch.append(int(step.last_n_unique.item()))
     graphed = None
     if not sharded and not a.no_graph:
         from easydl_b200.step import GraphedStep
@@ -384,14 +394,6 @@ def run_b200_arm(a):
         else:
             step.run(ids_dev[i % nb], grad_dev)
 
-    # unique ids per batch (deterministic per batch buffer): read once, outside the timed region
-    U_batch = []
-    for i in range(nb):
-        if not sharded:
-            U_batch.append(int(step.dedup(ids_dev[i]).n_unique.item()))
-        else:
-            step.run(ids_dev[i], grad_dev)
-            U_batch.append(int(step.last_n_unique.item()))
     for i in range(a.warmup):
         one_step(i)
     barrier()
@@ -414,6 +416,34 @@ def run_b200_arm(a):
         dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
     ms_max = float(t_ms.item())
     value = B * world * a.steps / (ms_max * 1e-3)
+
+    # ---------------- the same K steps with the NEXT batch's dedup running beside this batch's lookup and
+    # update (SparseStep.run_prefetch: the ids of batch i + 1 are known while batch i trains, as an input
+    # pipeline knows them).  Same work per step, bit-identical results; this is the headline `value`, the
+    # strictly sequential step above is reported beside it.
+    sequential = None
+    if not sharded and graphed is not None and nb % 2 == 0 and not a.no_prefetch:
+        from easydl_b200.step import GraphedPrefetchRing
+        sequential = {"value": value, "ms_per_step": ms_max / a.steps}
+        ring = GraphedPrefetchRing(step, ids_dev, grad_dev)
+        for i in range(max(a.warmup, nb)):
+            ring.run()
+        while ring.pos != (a.warmup % nb):      # start the timed steps at the same batch as the sequential run
+            ring.run()
+        barrier()
+        r0 = torch.cuda.Event(enable_timing=True)
+        r1 = torch.cuda.Event(enable_timing=True)
+        if sampler:
+            sampler.active = True
+        r0.record()
+        for i in range(a.steps):
+            ring.run()
+        r1.record()
+        barrier()
+        if sampler:
+            sampler.active = False
+        ms_max = r0.elapsed_time(r1)
+        value = B * world * a.steps / (ms_max * 1e-3)
     U_mean = float(np.mean([U_batch[(a.warmup + i) % nb] for i in range(a.steps)]))
 
     # ---------------- per-phase timing (same K steps again, events between the phases)
@@ -523,6 +553,8 @@ def run_b200_arm(a):
             "config": config_for(a, world, U_mean, sharded, nb),
             "gpu_launches": step.launches_per_step * a.steps,
             "launch_mode": "cuda_graph" if graphed is not None else "eager",
+            "step_pipelining": ("dedup of batch i+1 (helper stream) beside lookup + update of batch i; ring of "
+                                f"{nb} captured graphs" if sequential is not None else "none: each step strictly after the last"),
             "clocks": clocks,
         }
         if phases:
@@ -545,6 +577,8 @@ def run_b200_arm(a):
             line["phases"]["lookup_gbs"] = lookup_b / t_lk / 1e9
             line["phases"]["lookup_frac"] = lookup_b / t_lk / 1e9 / peak
             line["phases"]["lookup_update_gbs_whole_step"] = (lookup_b + update_b) / (ms_max / a.steps * 1e-3) / 1e9
+        if sequential is not None:
+            line["sequential_step"] = sequential
         if parity is not None:
             line["parity"] = parity
         if sharded_phases is not None:

@@ -417,6 +417,45 @@ def test_update_launch_variants_agree(cuda, opt_name, dim):
     assert len(set(digests)) == 1, digests
 
 
+@pytest.mark.parametrize("opt_name", ["adagrad", "adam"])
+def test_prefetched_dedup_gives_the_same_bits(cuda, opt_name):
+    """SparseStep.run_prefetch (the next batch's dedup beside this batch's lookup and update), eagerly and
+    replayed from the graph ring, against the plain step: identical embeddings, rows and slots."""
+    from easydl_b200.criteo import CriteoSynthetic
+    from easydl_b200.optimizer import OptimizerSpec
+    from easydl_b200.parameters import ShardParameters
+    from easydl_b200.step import GraphedPrefetchRing, SparseStep
+    rows, B, dim, n, steps = [50_000] * 26, 4096, 32, 4, 9
+    opt = OptimizerSpec.adagrad() if opt_name == "adagrad" else OptimizerSpec.adam()
+    src = CriteoSynthetic(rows, B, alpha=1.1)
+    ids = [torch.from_numpy(src.ids(k)).to(cuda) for k in range(n)]
+    grad = torch.from_numpy(src.grad(dim, 0)).to(cuda)
+    outs = []
+    for mode in ("plain", "prefetch", "graph"):
+        P = ShardParameters(rows, dim, opt, device=cuda)
+        st = SparseStep(P, B)
+        ring = GraphedPrefetchRing(st, ids, grad) if mode == "graph" else None
+        if ring is not None:                      # the ring's two warm-up steps touched the state: start over
+            P.reset()
+        embs = []
+        for k in range(steps):
+            if mode == "plain":
+                e = st.run(ids[k % n], grad)
+            elif mode == "prefetch":
+                e = st.run_prefetch(ids[k % n], grad, ids[(k + 1) % n])
+            else:
+                e = ring.run()
+            embs.append(e.clone())
+        torch.cuda.synchronize()
+        outs.append((embs, [t.clone() for t in P.state_tensors()], P.step))
+    for other in outs[1:]:
+        assert other[2] == outs[0][2]
+        for a, b in zip(outs[0][0], other[0]):
+            assert torch.equal(a, b)
+        for a, b in zip(outs[0][1], other[1]):
+            assert torch.equal(a, b)
+
+
 def test_tuning_knobs_reject_bad_input(cuda):
     from easydl_b200 import _lib
     with pytest.raises(_lib.EdlError, match="unknown knob"):
