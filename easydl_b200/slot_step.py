@@ -226,6 +226,7 @@ class SlotShardedStep:
         self.overlap = os.environ.get("EDL_SLOT_OVERLAP", "1") == "1"
         self.side = torch.cuda.Stream(device=dev, priority=-1) if self.overlap else None
         self.side2 = torch.cuda.Stream(device=dev) if self.overlap else None
+        self.side3 = torch.cuda.Stream(device=dev) if self.overlap else None
         self._prepared = None
         self.part = None
         self.last_n_unique = self.uq.n_unique
@@ -265,12 +266,15 @@ class SlotShardedStep:
             self._gather_for(self.rank)
             return
         cur = torch.cuda.current_stream()
-        self.side2.wait_stream(cur)
-        with torch.cuda.stream(self.side2):
-            for s in ring:
-                self._gather_for(s)
+        lanes = [self.side2, self.side3] if len(ring) > 1 else [self.side2]
+        for j, st in enumerate(lanes):       # two requesters in flight: one gather's tail under the other's body
+            st.wait_stream(cur)
+            with torch.cuda.stream(st):
+                for s in ring[j::len(lanes)]:
+                    self._gather_for(s)
         self._gather_for(self.rank)
-        cur.wait_stream(self.side2)
+        for st in lanes:
+            cur.wait_stream(st)
 
     def phase_c_expand(self) -> torch.Tensor:
         b, g, uq, part = self.buf, self.gen, self.uq, self.part
