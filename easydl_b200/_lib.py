@@ -63,6 +63,7 @@ PROTOTYPES = {
     "edl_lazy_gather": (_int, [_p, _i64, _p, _int, _i64, _p, _i64, _p, _p, C.c_uint64, _p, _p]),
     "edl_lazy_insert": (_int, [_p, _i64, _p, _p, _p, _int, _i64, _i64, _p, _i64, _p, _p, C.c_uint64,
                                C.c_float, C.c_float, _p, _p]),
+    "edl_lazy_stamp": (_int, [_p, _p, _i64, _p, C.c_int32, _p]),
     "edl_lazy_status_ptr": (_p, [_p, _i64]),
     "edl_lazy_dump": (_int, [_p, _i64, _p, _p, _p]),
     "edl_peer_alloc": (_int, [C.POINTER(C.c_void_p), _sz]),

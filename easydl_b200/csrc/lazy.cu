@@ -244,6 +244,29 @@ extern "C" int edl_lazy_insert(void* index, int64_t index_capacity, float* slab,
   return EDL_OK;
 }
 
+// stamps[slots[i]] = value for the rows of one update (i < *n_dev): the "last updated at step" mark that
+// an eviction policy reads
+namespace {
+__global__ void __launch_bounds__(kThreads)
+k_lazy_stamp(int32_t* __restrict__ stamps, const int64_t* __restrict__ slots, int64_t n, const int32_t* n_dev,
+             int32_t value) {
+  int64_t ne = n;
+  if (n_dev) { int64_t m = *n_dev; ne = m < n ? m : n; }
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < ne; i += (int64_t)gridDim.x * kThreads)
+    stamps[slots[i]] = value;
+}
+}  // namespace
+
+extern "C" int edl_lazy_stamp(int32_t* stamps, const int64_t* slots, int64_t n, const int32_t* n_dev, int32_t value,
+                              edl_stream_t stream) {
+  EDL_REQUIRE(n >= 0, EDL_EINVAL, "edl_lazy_stamp: n negative");
+  if (n == 0) return EDL_OK;
+  EDL_REQUIRE(stamps && slots, EDL_EINVAL, "edl_lazy_stamp: null pointer");
+  k_lazy_stamp<<<grid_for(n), kThreads, 0, (cudaStream_t)stream>>>(stamps, slots, n, n_dev, value);
+  EDL_LAUNCH_CHECK("k_lazy_stamp");
+  return EDL_OK;
+}
+
 // count (rows materialised) and err (1 = slab or index full) as a device int32[2]
 extern "C" const int32_t* edl_lazy_status_ptr(const void* index, int64_t index_capacity) {
   if (!index || !pow2(index_capacity)) return nullptr;

@@ -291,6 +291,10 @@ int edl_lazy_insert(void* index, int64_t index_capacity, float* slab, float* slo
                     int dim, int64_t row_stride, int64_t max_rows, const int64_t* keys, int64_t n, const int32_t* n_dev,
                     const int64_t* layout, uint64_t seed, float slot0_init, float slot1_init,
                     int64_t* slots_out, edl_stream_t stream);
+/* stamps[slots[i]] = value for i < *n_dev: marks the rows of one update (slots = edl_lazy_insert's output)
+ * with the step number, for an eviction policy that drops the rows not updated for longest. */
+int edl_lazy_stamp(int32_t* stamps, const int64_t* slots, int64_t n, const int32_t* n_dev, int32_t value,
+                   edl_stream_t stream);
 const int32_t* edl_lazy_status_ptr(const void* index, int64_t index_capacity);
 int edl_lazy_dump(const void* index, int64_t index_capacity, int64_t* keys_out, int64_t* slots_out,
                   edl_stream_t stream);

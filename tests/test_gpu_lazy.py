@@ -158,3 +158,92 @@ def test_slot_step_on_lazy_shards(cuda, opt, wire):
             _close(rec.slots[i].numpy(), o.slots[i], f"slot {i}")
     for b in bufs:
         b.close()
+
+
+def _lazy_trained(cuda, max_rows, steps=3, opt="adam"):
+    from easydl_b200.lazy_parameters import LazyShardParameters
+    from easydl_b200.optimizer import OptimizerSpec
+    from easydl_b200 import kernels as K
+    rows, dim, B = [3_000_000] * 4, 16, 512
+    po = OptimizerSpec.adam() if opt == "adam" else OptimizerSpec.adagrad()
+    P = LazyShardParameters(rows, dim, po, max_rows=max_rows, device=cuda)
+    bases = O.key_bases(rows)
+    batches = []
+    for k in range(steps):
+        _, ids, _ = O.criteo_batch(rows, B, 1.05, step=k)
+        g = O.synthetic_grad(ids.size, dim, step=k)
+        batches.append((dev(O.fuse_keys(ids, bases).reshape(-1), cuda), dev(g, cuda)))
+    return P, batches, K
+
+
+def _apply(P, K, keys, g):
+    uq = K.unique(keys, None, P.layout.key_bits, want_inverse=False, want_counts=False)
+    P.apply_gradients(uq, g)
+
+
+def test_lazy_shard_grows_without_changing_results(cuda):
+    """8(f).3 growth: a shard that runs out of room is re-housed in a larger slab between steps; rows, slots,
+    stamps and the step move, and training continues bit-identically to a shard that was large from the start."""
+    big, batches, K = _lazy_trained(cuda, 1 << 15)
+    small, _, _ = _lazy_trained(cuda, 1536)
+    for keys, g in batches[:2]:
+        _apply(big, K, keys, g)
+        small.ensure_room(keys.numel())           # grows when the next batch might not fit
+        _apply(small, K, keys, g)
+    assert small.max_rows > 1536
+    small.grow(small.max_rows * 2)
+    for keys, g in batches[2:]:
+        _apply(big, K, keys, g)
+        _apply(small, K, keys, g)
+    a, b = big.export_records(), small.export_records()
+    assert torch.equal(a.keys, b.keys) and torch.equal(a.rows, b.rows) and a.step == b.step
+    for x, y in zip(a.slots, b.slots):
+        assert torch.equal(x, y)
+
+
+def test_lazy_shard_eviction_and_return(cuda):
+    """8(f).3 eviction: rows not updated since a cut-off step leave the slab and are handed back; the rest
+    stays put; re-importing the evicted records restores the shard bit for bit."""
+    P, batches, K = _lazy_trained(cuda, 1 << 15)
+    for keys, g in batches:
+        _apply(P, K, keys, g)
+    before = P.export_records()
+    n0 = P.materialised()
+    gone = P.evict_older_than(3)                  # keep only what step 3 touched
+    assert 0 < len(gone) < n0 and P.materialised() == n0 - len(gone) and gone.step == before.step
+    kept = P.export_records()
+    both = torch.cat([kept.keys, gone.keys]).sort().values
+    assert torch.equal(both, before.keys)
+    # an evicted key reads as its initial value again (lossy unless re-imported)
+    fresh = P.lookup(gone.keys[:8].contiguous())
+    t, ids = O.split_key(gone.keys[:8].cpu().numpy(), O.key_bases([3_000_000] * 4))
+    want = np.stack([O.init_rows(O.DEFAULT_SEED, int(tt), np.array([ii]), 16)[0] for tt, ii in zip(t, ids)])
+    assert np.array_equal(bits(fresh.cpu().numpy()), bits(want))
+    P.import_records(gone)
+    after = P.export_records()
+    assert torch.equal(after.keys, before.keys) and torch.equal(after.rows, before.rows)
+    for x, y in zip(after.slots, before.slots):
+        assert torch.equal(x, y)
+
+
+def test_lazy_shard_raw_checkpoint_restores_index_and_slab(cuda, tmp_path):
+    """8(f).3 index checkpoint: save_raw / load_raw bring back the hash index, the slab prefix, the stamps and
+    the step as they lay -- no key is re-inserted -- and training continues bit-identically."""
+    from easydl_b200.lazy_parameters import LazyShardParameters
+    P, batches, K = _lazy_trained(cuda, 1 << 14)
+    for keys, g in batches[:2]:
+        _apply(P, K, keys, g)
+    path = str(tmp_path / "shard0.raw")
+    P.save_raw(path)
+    Q = LazyShardParameters([3_000_000] * 4, 16, P.opt, max_rows=1 << 12, device=cuda)   # other size: re-allocated
+    Q.load_raw(path)
+    assert Q.step == P.step and Q.materialised() == P.materialised()
+    assert torch.equal(Q.index, P.index) and torch.equal(Q.stamp[:P.materialised()], P.stamp[:P.materialised()])
+    keys, g = batches[2]
+    _apply(P, K, keys, g)
+    _apply(Q, K, keys, g)
+    a, b = P.export_records(), Q.export_records()
+    assert torch.equal(a.keys, b.keys) and torch.equal(a.rows, b.rows)
+    for x, y in zip(a.slots, b.slots):
+        assert torch.equal(x, y)
+    assert torch.equal(P.lookup(keys), Q.lookup(keys))
