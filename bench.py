@@ -541,6 +541,30 @@ def run_b200_arm(a):
                "ms_per_step": float(t2.item()) / a.e2e_steps,
                "path": "HostStepRunner: ids H2D -> lookup -> emb D2H (stream 1) || grad H2D (stream 2) -> dedup + update -> n_unique D2H"}
 
+    # ---------------- the same through the lineage API itself (N = 1): PSClient.pull_embedding_batch (host ids
+    # -> host embeddings) + push_gradient_batch (host gradients), one in-process PS shard over the same tables
+    lineage = None
+    if not a.no_e2e and not sharded:
+        from easydl_b200.ps import ParameterServer
+        from easydl_b200.ps_client import PSClient
+        ps = ParameterServer([f"C{i + 1}" for i in range(F)], rows, D, opt, params=params)
+        client = PSClient([ps])
+        g3 = grad_host.view(B, F, D)
+        for i in range(2):
+            client.pull_embedding_batch(ids_host[i % nb])
+            client.push_gradient_batch(g3)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(a.e2e_steps):
+            client.pull_embedding_batch(ids_host[i % nb])
+            client.push_gradient_batch(g3)
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / a.e2e_steps
+        lineage = {"value": B / dt, "unit": UNIT, "ms_per_step": dt * 1e3,
+                   "path": "PSClient.pull_embedding_batch -> PSClient.push_gradient_batch (pinned host arrays in and "
+                           "out, one wait per pull, none per push); host wall clock"}
+        del client, ps
+
     clocks = sampler.result() if sampler else None
 
     if rank == 0:
@@ -587,6 +611,8 @@ def run_b200_arm(a):
             line["roofline"] = sharded_roofline(a, world, N, U_mean, owner_counts, ms_max / a.steps, peak, peak_kind)
         if e2e:
             line["e2e"] = e2e
+        if lineage:
+            line["e2e_lineage_api"] = lineage
         if not a.no_cpu_baseline:
             v, spp = cpu_reference(a, 1, a.cpu_steps, 1)
             line["cpu_baseline"] = {

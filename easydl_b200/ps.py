@@ -50,9 +50,11 @@ class ParameterServer:
     (the client partitions with int_to_id)."""
 
     def __init__(self, table_names: Sequence[str], rows: Sequence[int], dim: int, opt: OptimizerSpec,
-                 num_shards: int = 1, shard: int = 0, seed: int = DEFAULT_SEED, device="cuda:0"):
+                 num_shards: int = 1, shard: int = 0, seed: int = DEFAULT_SEED, device="cuda:0", params=None):
+        # params: serve an existing ShardParameters / LazyShardParameters instead of allocating tables
         self.names = list(table_names)
-        self.embedding_params = ShardParameters(rows, dim, opt, num_shards, shard, seed=seed, device=device)
+        self.embedding_params = params if params is not None else \
+            ShardParameters(rows, dim, opt, num_shards, shard, seed=seed, device=device)
         self.tables: Dict[str, EmbeddingTable] = {
             n: EmbeddingTable(self.embedding_params, i, n) for i, n in enumerate(self.names)}
         self.non_embedding_params: Dict[str, torch.Tensor] = {}

@@ -72,6 +72,39 @@ class PSClient:
         self.layout_dev = p0.layout_dev
         self.field_base = torch.from_numpy(p0.layout.key_base[:-1].copy()).to(self.device)
         self._last = None
+        self._fast = None          # S == 1: buffers of the synchronisation-free batch path
+
+    # ---- S == 1: one PS shard in this process.  No dedup is needed to look rows up, nothing has to be
+    # partitioned, and no size has to come back to the host: ids go up, rows come down into a pinned buffer,
+    # gradients go up and the dedup + reduce + optimizer are enqueued behind them.  The only host wait is the
+    # one the caller asked for (the embeddings of pull_embedding_batch).
+    def _fast_buffers(self, B: int, F: int):
+        from .step import SparseStep
+        key = (B, F)
+        if self._fast is None or self._fast["key"] != key:
+            p = self.servers[0].embedding_params
+            step = SparseStep(p, B, F, overlap_dedup=False)
+            self._fast = {"key": key, "step": step,
+                          "ids": torch.empty((B, F), dtype=torch.int64, device=self.device),
+                          "grad": torch.empty((B * F, p.dim), dtype=torch.float32, device=self.device),
+                          "emb_host": torch.empty((B * F, p.dim), dtype=torch.float32).pin_memory(),
+                          "done": torch.cuda.Event()}
+        return self._fast
+
+    def _pull_batch_fast(self, ids_t: torch.Tensor):
+        B, F = ids_t.shape
+        f = self._fast_buffers(B, F)
+        f["ids"].copy_(ids_t, non_blocking=True)
+        emb = f["step"].lookup(f["ids"])
+        f["emb_host"].copy_(emb, non_blocking=True)
+        f["done"].record()
+        f["done"].synchronize()                      # the caller gets host data: the one wait of the call
+        return f["emb_host"].numpy().reshape(B, F, -1)   # a view of the pinned buffer, valid until the next pull
+
+    def _push_batch_fast(self, g_t: torch.Tensor):
+        f = self._fast
+        f["grad"].copy_(g_t.reshape(f["grad"].shape), non_blocking=True)
+        f["step"].update(f["ids"], f["grad"])        # dedup + reduce + optimizer, enqueued; no host wait
 
     # ---- helpers
     def _pull_keys(self, flat_ids_dev, field_base):
@@ -106,6 +139,9 @@ class PSClient:
         the matching push_gradient_batch."""
         ids_t = torch.as_tensor(ids, dtype=torch.int64)
         B, F = ids_t.shape
+        if self.S == 1 and self.servers[0].embedding_params.num_shards == 1:
+            self._last = "fast"
+            return self._pull_batch_fast(ids_t)
         emb, st = self._pull_keys(ids_t.to(self.device).reshape(-1), self.field_base[:F].contiguous())
         self._last = st
         return emb.cpu().numpy().reshape(B, F, -1)
@@ -113,6 +149,8 @@ class PSClient:
     def push_gradient_batch(self, grads):
         """grads: host [B, F, dim], gradient of the last pull_embedding_batch's output."""
         from . import kernels as K
+        if self._last == "fast":
+            return self._push_batch_fast(torch.as_tensor(grads, dtype=torch.float32))
         uq, U, keys_by, offs, pos = self._last
         g = torch.as_tensor(grads, dtype=torch.float32).reshape(uq.n, -1).to(self.device)
         g_send = torch.empty((max(U, 1), g.shape[1]), dtype=torch.float64, device=self.device)
