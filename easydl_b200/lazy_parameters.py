@@ -110,6 +110,11 @@ class LazyShardParameters:
 
     _RING = 1024
 
+    @property
+    def rate_changes(self) -> bool:
+        from ._lib import EDL_OPT_ADAM
+        return self.opt.kind == EDL_OPT_ADAM
+
     def stage_rate(self, step: int):
         """rate(step) -> lr_dev on the current stream (same contract as ShardParameters.stage_rate)."""
         if self._lr_ring is None:

@@ -107,6 +107,13 @@ class ShardParameters:
     # ------------------------------------------------------------------ A4 + A5
     _RING = 1024
 
+    @property
+    def rate_changes(self) -> bool:
+        """True if the optimizer rate differs from step to step (Adam's bias correction): a captured launch
+        sequence must then read it from lr_dev; a constant rate (Adagrad) is captured by value."""
+        from ._lib import EDL_OPT_ADAM
+        return self.opt.kind == EDL_OPT_ADAM
+
     def stage_rate(self, step: int):
         """Enqueue rate(step) -> lr_dev on the current stream (from a ring of pinned host slots, so the
         host never waits).  Call before replaying a launch sequence captured with rate_on_device."""

@@ -426,7 +426,7 @@ class GraphedSlotStep:
         self.graphs = [None, None]
         lanes = getattr(step, "lanes", [step])
         for l in lanes:
-            l.rate_on_device = True
+            l.rate_on_device = step.params.rate_changes
         try:
             for _ in (0, 1):                 # in the order the generations come up next
                 gen = step.gen
@@ -441,7 +441,8 @@ class GraphedSlotStep:
 
     def run(self) -> torch.Tensor:
         st = self.step                        # the generation lives on the step: several graphed
-        st.params.stage_rate(st.params.step + 1)
+        if st.params.rate_changes:
+            st.params.stage_rate(st.params.step + 1)
         self.graphs[st.gen].replay()          # (ids, grad) pairs may share one step
         st.gen ^= 1
         st.params.step += 1

@@ -147,15 +147,17 @@ class GraphedStep:
             step.lookup(ids)
         with torch.cuda.graph(self.g_dedup):
             step.dedup(ids)
+        dev_rate = step.params.rate_changes
         with torch.cuda.graph(self.g_update):
-            step.update(ids, grad, step.uq, rate_on_device=True)
+            step.update(ids, grad, step.uq, rate_on_device=dev_rate)
         with torch.cuda.graph(self.g_all):
-            step.run(ids, grad, rate_on_device=True)
+            step.run(ids, grad, rate_on_device=dev_rate)
         step.params.step = host_step
 
     def run(self):
         p = self.step.params
-        p.stage_rate(p.step + 1)
+        if p.rate_changes:
+            p.stage_rate(p.step + 1)
         self.g_all.replay()
         p.step += 1
         return self.step.emb
@@ -188,7 +190,8 @@ class GraphedPrefetchRing:
         for i in range(n):
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                step.run_prefetch(self.ids_ring[i], grad, self.ids_ring[(i + 1) % n], rate_on_device=True)
+                step.run_prefetch(self.ids_ring[i], grad, self.ids_ring[(i + 1) % n],
+                                  rate_on_device=step.params.rate_changes)
             self.graphs.append(g)
         step.params.step = host_step
         # capture ran the host-side buffer swaps n times (n even): the pair is back where it started, and
@@ -196,7 +199,8 @@ class GraphedPrefetchRing:
 
     def run(self):
         p = self.step.params
-        p.stage_rate(p.step + 1)
+        if p.rate_changes:
+            p.stage_rate(p.step + 1)
         self.graphs[self.pos].replay()
         self.pos = (self.pos + 1) % len(self.graphs)
         p.step += 1

@@ -119,9 +119,9 @@ def main():
                 with torch.cuda.graph(gd):
                     step.dedup(i)
                 with torch.cuda.graph(gu):
-                    step.update(i, grad, step.uq, rate_on_device=True)
+                    step.update(i, grad, step.uq, rate_on_device=P.rate_changes)
                 with torch.cuda.graph(ga):
-                    step.run(i, grad, rate_on_device=True)
+                    step.run(i, grad, rate_on_device=P.rate_changes)
                 graphs.append((gl, gd, gu, ga))
             P.step = host_step
 
@@ -131,7 +131,7 @@ def main():
                     g = graphs[k % len(graphs)]
                     if which == 2:
                         g[1].replay()         # the update reads the dedup of ITS batch
-                    if which >= 2:
+                    if which >= 2 and P.rate_changes:
                         P.stage_rate(P.step + 1)
                     if k >= 5:
                         ev[k - 5][0].record()
