@@ -422,6 +422,30 @@ def run_b200_arm(a):
     # pipeline knows them).  Same work per step, bit-identical results; this is the headline `value`, the
     # strictly sequential step above is reported beside it.
     sequential = None
+    if sharded and world > 1 and a.exchange == "slots" and graphed is not None and nb % 2 == 0 and not a.no_prefetch:
+        # sharded: phase A (dedup, partition, key send) of batch i + 1 beside the rounds of batch i
+        from easydl_b200.slot_step import GraphedSlotRing
+        sequential = {"value": value, "ms_per_step": ms_max / a.steps}
+        ring = GraphedSlotRing(step, ids_dev, grad_dev)
+        for i in range(max(a.warmup, nb)):
+            ring.run()
+        barrier()
+        r0 = torch.cuda.Event(enable_timing=True)
+        r1 = torch.cuda.Event(enable_timing=True)
+        if sampler:
+            sampler.active = True
+        r0.record()
+        for i in range(a.steps):
+            ring.run()
+        r1.record()
+        barrier()
+        if sampler:
+            sampler.active = False
+        step.check()
+        t_ms = torch.tensor([r0.elapsed_time(r1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+        ms_max = float(t_ms.item())
+        value = B * world * a.steps / (ms_max * 1e-3)
     if not sharded and graphed is not None and nb % 2 == 0 and not a.no_prefetch:
         from easydl_b200.step import GraphedPrefetchRing
         sequential = {"value": value, "ms_per_step": ms_max / a.steps}
@@ -578,8 +602,10 @@ def run_b200_arm(a):
             "config": config_for(a, world, U_mean, sharded, nb),
             "gpu_launches": step.launches_per_step * a.steps,
             "launch_mode": "cuda_graph" if graphed is not None else "eager",
-            "step_pipelining": ("dedup of batch i+1 (helper stream) beside lookup + update of batch i; ring of "
-                                f"{nb} captured graphs" if sequential is not None else "none: each step strictly after the last"),
+            "step_pipelining": (("phase A (dedup, partition, key send) of batch i+1 beside the rounds of batch i" if sharded
+                                 else "dedup of batch i+1 (helper stream) beside lookup + update of batch i") +
+                                f"; ring of {nb} captured graphs" if sequential is not None
+                                else "none: each step strictly after the last"),
             "clocks": clocks,
         }
         if phases:

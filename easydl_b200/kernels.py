@@ -149,17 +149,21 @@ class PartitionResult:
     pos: Optional[torch.Tensor]  # int32 [n] output position of each input
 
 
+def partition_buffers(n: int, num_shards: int, device, want_pos: bool = True) -> PartitionResult:
+    return PartitionResult(torch.empty(n, dtype=torch.int64, device=device),
+                           torch.empty(num_shards + 1, dtype=torch.int32, device=device),
+                           torch.empty(n, dtype=torch.int32, device=device),
+                           torch.empty(n, dtype=torch.int32, device=device) if want_pos else None)
+
+
 def partition_mod(keys: torch.Tensor, layout: Optional[torch.Tensor], num_shards: int, *,
                   n_dev: Optional[torch.Tensor] = None, want_pos: bool = True,
-                  workspace: Optional[torch.Tensor] = None) -> PartitionResult:
+                  workspace: Optional[torch.Tensor] = None, out: Optional[PartitionResult] = None) -> PartitionResult:
     lib = _lib.load()
     _need(keys, torch.int64, "keys")
     n = keys.numel()
     dev = keys.device
-    res = PartitionResult(torch.empty(n, dtype=torch.int64, device=dev),
-                          torch.empty(num_shards + 1, dtype=torch.int32, device=dev),
-                          torch.empty(n, dtype=torch.int32, device=dev),
-                          torch.empty(n, dtype=torch.int32, device=dev) if want_pos else None)
+    res = out if out is not None else partition_buffers(n, num_shards, dev, want_pos)
     need = lib.edl_partition_mod_workspace_bytes(n, num_shards)
     if workspace is None or workspace.numel() < need:
         workspace = _ws(need, dev)

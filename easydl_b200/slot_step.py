@@ -228,7 +228,12 @@ class SlotShardedStep:
         self.side2 = torch.cuda.Stream(device=dev) if self.overlap else None
         self.side3 = torch.cuda.Stream(device=dev) if self.overlap else None
         self._prepared = None
-        self.part = None
+        self.part = K.partition_buffers(N, self.S, dev)
+        # second front (dedup + partition results) for run_prefetch: the NEXT batch's phase A beside this step
+        self.uq_next = None
+        self.part_next = None
+        self.side_pf = None
+        self._ahead = None
         self.last_n_unique = self.uq.n_unique
         passes1 = min((self.key_bits + 7) // 8, (self.field_bits + 7) // 8) if self.field_bits else (self.key_bits + 7) // 8
         passes2 = (self.key_bits + 7) // 8
@@ -237,17 +242,20 @@ class SlotShardedStep:
         self.launches_per_step = (3 * passes1 + 3) + 4 + 1 + self.S + 3 + 2 + 4 + 1 + (3 * passes2 + 3) + 2 + 4 + 3
 
     # ------------------------------------------------------------------ phases
-    def phase_a(self, ids: torch.Tensor):
-        b, g = self.buf, self.gen
+    def phase_a(self, ids: torch.Tensor, front=None, gen: Optional[int] = None):
+        """front = (UniqueResult, PartitionResult) to fill and gen = the buffer generation to send into
+        (defaults: this step's own).  run_prefetch passes the second front and the other generation."""
+        b = self.buf
+        g = self.gen if gen is None else gen
+        uq, part = (self.uq, self.part) if front is None else front
         K.unique(ids.reshape(-1), self.field_base, self.key_bits, field_bits=self.field_bits, want_inverse=True,
-                 want_counts=False, out=self.uq, workspace=self.ws_u1)
-        self.part = K.partition_mod(self.uq.uniq, self.params.layout_dev, self.S, n_dev=self.uq.n_unique,
-                                    workspace=self.ws_part)
-        K.slot_send(self.part.keys, self.part.offsets, b.keys_dst[g], self.limit, b.count_dst[g], b.err, self.N,
-                    flag_seg=self.uq.seg_offsets if self.mixed else None, flag_perm=self.part.perm if self.mixed else None)
+                 want_counts=False, out=uq, workspace=self.ws_u1)
+        K.partition_mod(uq.uniq, self.params.layout_dev, self.S, n_dev=uq.n_unique, workspace=self.ws_part, out=part)
+        K.slot_send(part.keys, part.offsets, b.keys_dst[g], self.limit, b.count_dst[g], b.err, self.N,
+                    flag_seg=uq.seg_offsets if self.mixed else None, flag_perm=part.perm if self.mixed else None)
         if self.windowed:
-            K.remap_index(self.uq.order, self.grad_map, None, out=self.order_w)
-            K.remap_index(self.uq.seg_first, self.grad_map, self.uq.n_unique, out=self.first_w)
+            K.remap_index(uq.order, self.grad_map, None, out=self.order_w)
+            K.remap_index(uq.seg_first, self.grad_map, uq.n_unique, out=self.first_w)
 
     def _gather_for(self, s: int):
         b, g = self.buf, self.gen
@@ -354,6 +362,47 @@ class SlotShardedStep:
         self.update(ids, grad)
         return emb
 
+    def run_prefetch(self, ids: torch.Tensor, grad: torch.Tensor, next_ids: torch.Tensor) -> torch.Tensor:
+        """One step with phase A of the NEXT batch (dedup, partition, key send into the other buffer
+        generation) on a helper stream beside this step's rounds -- the ids of batch k + 1 are known while
+        batch k trains.  Safe from fence 1 on: every peer has then finished step k - 1, the last reader of
+        that generation's key slots.  Same work per step, same results.  Every rank must use it in lock step
+        with the same batch order; not for the lanes of PipelinedSlotStep."""
+        if self.windowed:
+            raise ValueError("run_prefetch is for the unpipelined slot step")
+        if self.uq_next is None:
+            N, dev = self.N, self.device
+            i32 = dict(dtype=torch.int32, device=dev)
+            self.uq_next = K.UniqueResult(
+                uniq=torch.empty(N, dtype=torch.int64, device=dev), inverse=torch.empty(N, **i32), counts=None,
+                order=torch.empty(N, **i32), seg_offsets=torch.empty(N + 1, **i32),
+                n_unique=torch.zeros(1, **i32), n=N, seg_first=torch.empty(N, **i32))
+            self.part_next = K.partition_buffers(N, self.S, dev)
+            self.side_pf = torch.cuda.Stream(device=dev, priority=-1)
+        cur = torch.cuda.current_stream()
+        if self._ahead != ids.data_ptr():
+            self.phase_a(ids)                               # first step: this batch's own phase A
+        self.buf.fence()
+        if self.overlap:
+            self.side.wait_stream(cur)
+            with torch.cuda.stream(self.side):
+                self.phase_d_prepare()
+                self._prepared = torch.cuda.Event()
+                self._prepared.record()
+        self.side_pf.wait_stream(cur)
+        with torch.cuda.stream(self.side_pf):
+            self.phase_a(next_ids, front=(self.uq_next, self.part_next), gen=self.gen ^ 1)
+        self.phase_b(self.overlap)
+        self.buf.fence()
+        emb = self.phase_c_expand()
+        self.update(ids, grad)
+        cur.wait_stream(self.side_pf)                       # the next step's keys are sent before its fence 1
+        self.uq, self.uq_next = self.uq_next, self.uq
+        self.part, self.part_next = self.part_next, self.part
+        self.last_n_unique = self.uq.n_unique
+        self._ahead = next_ids.data_ptr()
+        return emb
+
     PHASES = ("A_dedup_partition_send", "fence1", "B_owner_gather", "fence2", "C_expand", "C_reduce_send", "fence3",
               "D_owner_dedup", "D_owner_update")
 
@@ -444,6 +493,52 @@ class GraphedSlotStep:
         if st.params.rate_changes:
             st.params.stage_rate(st.params.step + 1)
         self.graphs[st.gen].replay()          # (ids, grad) pairs may share one step
+        st.gen ^= 1
+        st.params.step += 1
+        return st.emb
+
+
+class GraphedSlotRing:
+    """SlotShardedStep.run_prefetch over a fixed ring of id buffers (even length) and one gradient buffer,
+    one CUDA graph per ring position.  Two eager steps (ring positions 0 and 1) come first -- they are real
+    steps -- and the graphs are captured from position 2 on, in the order they will be replayed, so buffer
+    generations, fronts and the keys already sent for the next step line up.  Every rank constructs and
+    replays in lock step."""
+
+    def __init__(self, step: SlotShardedStep, ids_ring, grad: torch.Tensor):
+        n = len(ids_ring)
+        if n % 2 or n < 2:
+            raise ValueError("the ring of id batches must have an even length")
+        self.step, self.ids_ring, self.grad = step, list(ids_ring), grad
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            for i in (0, 1):
+                step.run_prefetch(self.ids_ring[i], grad, self.ids_ring[(i + 1) % n])
+        cur.wait_stream(side)
+        torch.cuda.synchronize()
+        host_step = step.params.step
+        step.rate_on_device = step.params.rate_changes
+        self.graphs = [None] * n
+        try:
+            for k in range(n):
+                i = (2 + k) % n
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    step.run_prefetch(self.ids_ring[i], grad, self.ids_ring[(i + 1) % n])
+                self.graphs[i] = g
+        finally:
+            step.rate_on_device = False
+        step.params.step = host_step
+        self.pos = 2 % n
+
+    def run(self) -> torch.Tensor:
+        st = self.step
+        if st.params.rate_changes:
+            st.params.stage_rate(st.params.step + 1)
+        self.graphs[self.pos].replay()
+        self.pos = (self.pos + 1) % len(self.graphs)
         st.gen ^= 1
         st.params.step += 1
         return st.emb

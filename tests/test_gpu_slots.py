@@ -307,3 +307,48 @@ def test_real_drivers_world_of_one_eager_equals_graph(cuda, n_lanes):
     assert torch.equal(p1.slab, p3.slab) and torch.equal(p1.slots[0], p3.slots[0])
     for b in b1 + b2 + [b3]:
         b.close()
+
+
+@pytest.mark.parametrize("opt_name,wire", [("adagrad", "mixed"), ("adam", torch.float64)])
+def test_prefetching_slot_step_world_of_one(cuda, opt_name, wire):
+    """SlotShardedStep.run_prefetch (the next batch's phase A on a helper stream, sent into the other buffer
+    generation) eagerly and replayed from GraphedSlotRing, against plain eager steps over the same batch
+    sequence: identical embeddings, rows and slots.  World of one: the fences are real kernels."""
+    from easydl_b200.optimizer import OptimizerSpec
+    from easydl_b200.parameters import ShardParameters
+    from easydl_b200.slot_step import GraphedSlotRing, SlotBuffers, SlotShardedStep
+    rows, dim, batch, n, steps = [20000, 3000, 17, 900], 32, 1024, 4, 10
+    F = len(rows)
+    ids = [dev(O.criteo_batch(rows, batch, 1.1, step=k)[1], cuda) for k in range(n)]
+    g = dev(O.synthetic_grad(batch * F, dim, step=0), cuda)
+    po = OptimizerSpec.adagrad() if opt_name == "adagrad" else OptimizerSpec.adam()
+    outs = []
+    for mode in ("plain", "prefetch", "ring"):
+        p = ShardParameters(rows, dim, po, 1, 0, device=cuda)
+        b = SlotBuffers(1, 0, cuda, batch * F, dim, wire)
+        b.connect_local([b])
+        st = SlotShardedStep(p, batch, b, wire_dtype=wire)
+        embs = []
+        ring = None
+        for k in range(steps):
+            if mode == "plain":
+                e = st.run(ids[k % n], g)
+            elif mode == "prefetch":
+                e = st.run_prefetch(ids[k % n], g, ids[(k + 1) % n])
+            else:
+                if ring is None:
+                    ring = GraphedSlotRing(st, ids, g)          # runs steps 0 and 1 eagerly
+                    embs += [None, None]
+                if k < 2:
+                    continue
+                e = ring.run()
+            embs.append(e.clone())
+        st.check()
+        outs.append((embs, [t.clone() for t in p.state_tensors()], p.step))
+        b.close()
+    for other in outs[1:]:
+        assert other[2] == outs[0][2] == steps
+        for a, c in zip(outs[0][0], other[0]):
+            assert c is None or torch.equal(a, c)
+        for a, c in zip(outs[0][1], other[1]):
+            assert torch.equal(a, c)

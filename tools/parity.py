@@ -70,10 +70,12 @@ def check_exchange(kind: str, dev, group=None, wire_dtype=torch.float64, lanes: 
         oo = O.OptimizerSpec.adam() if opt_name == "adam" else O.OptimizerSpec.adagrad()
         P = params_factory(po) if params_factory else ShardParameters(ROWS, DIM, po, world, rank, device=dev)
         st, ex = _make_step(kind, P, group, dev, wire_dtype, lanes)
-        embs, last = [], None
+        embs, last, prev_ids = [], None, None
         for k in range(STEPS):
             _, ids, _ = O.criteo_batch(ROWS, BATCH, 1.05, step=k * world + rank)
             g = O.synthetic_grad(ids.size, DIM, step=k * world + rank)
+            if last is not None:
+                prev_ids = last[0]
             last = (torch.from_numpy(ids).to(dev), torch.from_numpy(g).to(dev))
             embs.append(st.run(*last).cpu().numpy())
         torch.cuda.synchronize()
@@ -123,6 +125,29 @@ def check_exchange(kind: str, dev, group=None, wire_dtype=torch.float64, lanes: 
                 del st2, P2
             same = torch.equal(states[0][0], states[1][0]) and torch.equal(states[0][1], states[1][1]) and \
                 states[0][3] == states[1][3] and all(torch.equal(a, b) for a, b in zip(states[0][2], states[1][2]))
+            if kind == "slots":
+                # and the prefetching ring (next batch's phase A beside this step; two eager + two replayed steps
+                # over two different batches) == four plain eager steps over the same batch sequence
+                from easydl_b200.slot_step import GraphedSlotRing
+                ring_ids = [prev_ids, ids_d]
+                rstates = []
+                for use_ring in (False, True):
+                    P3 = params_factory(po) if params_factory else ShardParameters(ROWS, DIM, po, world, rank, device=dev)
+                    st3, _ = _make_step(kind, P3, group, dev, wire_dtype, lanes)
+                    if use_ring:
+                        ring = GraphedSlotRing(st3, ring_ids, g_d)
+                        ring.run()
+                        ring.run()
+                    else:
+                        for k in range(4):
+                            st3.run(ring_ids[k % 2], g_d)
+                    st3.check()
+                    r3 = P3.export_records()
+                    rstates.append((r3.keys.clone(), r3.rows.clone(), [x.clone() for x in r3.slots], P3.step))
+                    _close(st3, None)
+                    del st3, P3
+                same = same and torch.equal(rstates[0][0], rstates[1][0]) and torch.equal(rstates[0][1], rstates[1][1]) \
+                    and rstates[0][3] == rstates[1][3] and all(torch.equal(a, b) for a, b in zip(rstates[0][2], rstates[1][2]))
             graph_equal = same if graph_equal is None else (graph_equal and same)
             ok &= same
     flag = torch.tensor([1 if ok else 0], device=dev)
