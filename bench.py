@@ -194,7 +194,7 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------ CPU arm
-def cpu_reference(a, threads: int, steps: int, warmup: int):
+def cpu_reference(a, threads: int, steps: int, warmup: int, nb_max: int = 2, state=None):
     """The CPU parameter-server path (oracle port) on the host cores.  Tables are lazily
     materialised; one untimed pass per distinct batch creates the rows so the timed steps
     measure lookup + reduce + update, not row initialisation."""
@@ -204,8 +204,12 @@ def cpu_reference(a, threads: int, steps: int, warmup: int):
     rows = [a.rows] * N_FIELDS
     opt = O.OptimizerSpec.adagrad() if a.optimizer == "adagrad" else O.OptimizerSpec.adam()
     shard = O.OracleShard(rows, a.dim, opt)
-    nb = max(1, min(a.n_batches, 2))
+    nb = max(1, min(a.n_batches, nb_max))
     batches = [O.criteo_batch(rows, a.batch, a.alpha, step=i)[1] for i in range(nb)]
+    if state is not None:      # unique ids per step over the steps that will be timed (as the GPU arm counts them)
+        u = [len(np.unique(O.fuse_keys(b, shard.bases))) for b in batches]
+        state["nb"] = nb
+        state["U_of"] = lambda w, k: float(np.mean([u[(w + i) % nb] for i in range(k)]))
     grad = O.synthetic_grad(a.batch * N_FIELDS, a.dim)
     for ids in batches:  # materialise
         shard.materialise(np.unique(O.fuse_keys(ids, shard.bases)))
@@ -214,23 +218,22 @@ def cpu_reference(a, threads: int, steps: int, warmup: int):
         O.sparse_step_per_table(shard, batches[i % nb], grad, pool)
     t0 = time.perf_counter()
     for i in range(steps):
-        O.sparse_step_per_table(shard, batches[i % nb], grad, pool)
+        O.sparse_step_per_table(shard, batches[(warmup + i) % nb], grad, pool)
     dt = time.perf_counter() - t0
     return a.batch * steps / dt, dt / steps
 
 
-def config_for(a, world, U_mean=None, sharded=False, nb=None):
-    """The `config` object of the JSON line: the same keys on both arms."""
+def config_for(a, world, U_mean=None, nb=None):
+    """The `config` object of the JSON line: the WORKLOAD only, so that both arms print the same object
+    (how an arm runs it goes into `implementation`)."""
     F, D, B = N_FIELDS, a.dim, a.batch
     N = B * F
     table_gb = F * a.rows * D * 4 / 1e9
     slots = 1 if a.optimizer == "adagrad" else 2
     return {"workload": workload_name(a), "global_batch": B * world, "tables": F, "rows_per_table": a.rows,
-            "dim": D, "zipf_alpha": a.alpha, "optimizer": a.optimizer, "unique_per_step": U_mean,
+            "dim": D, "zipf_alpha": a.alpha, "optimizer": a.optimizer,
+            "unique_per_step": None if U_mean is None else round(float(U_mean), 1),
             "sharding": f"row-wise id mod {world}",
-            "code_path": ("sharded, lazily materialised rows" if getattr(a, "lazy_rows", 0) else "sharded") if sharded else "single-shard fused",
-            "gradient_wire": a.wire if sharded else None,
-            "exchange": (a.exchange if world > 1 else None),
             "cache": f"inputs larger than L2: {table_gb * (1 + slots):.0f} GB of table + optimizer rows touched at "
                      f"random, {nb if nb else a.n_batches} id batches cycled, {N * D * 4 / 1e6:.0f} MB gradient + "
                      f"{N * D * 4 / 1e6:.0f} MB output per GPU per step"}
@@ -247,17 +250,17 @@ def run_reference_arm(a):
     budget_s = 150.0
     steps = max(1, min(a.steps, int(budget_s / max(probe_spp, 1e-3))))
     warm = max(0, min(a.warmup, int(0.2 * budget_s / max(probe_spp, 1e-3))))
-    v, spp = cpu_reference(a, threads, steps, warm)
+    st = {}
+    v, spp = cpu_reference(a, threads, steps, warm, nb_max=a.n_batches, state=st)
     sample = (f"{steps} full steps (batch {a.batch}, {N_FIELDS} tables, dim {a.dim}) of the NumPy oracle, "
               f"one table per thread on {threads} threads, rows pre-materialised")
-    cfg = config_for(a, a.gpus, None, False, min(a.n_batches, 2))
-    cfg["code_path"] = "CPU parameter-server path (oracle port), one host, all cores; the GPUs are unused"
-    cfg["exchange"] = None
+    cfg = config_for(a, a.gpus, st["U_of"](warm, steps), st["nb"])
     line = {
         "metric": METRIC, "value": v, "unit": UNIT, "impl": "reference", "n_gpus": a.gpus,
         "steps": steps, "warmup": warm, "ms_per_step": spp * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": cfg,
+        "implementation": {"code_path": "CPU parameter-server path (oracle port), one host, all cores; the GPUs are unused"},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -599,7 +602,10 @@ def run_b200_arm(a):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": ms_max / a.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": config_for(a, world, U_mean, sharded, nb),
+            "config": config_for(a, world, U_mean, nb),
+            "implementation": {
+                "code_path": ("sharded, lazily materialised rows" if a.lazy_rows else "sharded") if sharded else "single-shard fused",
+                "gradient_wire": a.wire if sharded else None, "exchange": (a.exchange if world > 1 else None)},
             "gpu_launches": step.launches_per_step * a.steps,
             "launch_mode": "cuda_graph" if graphed is not None else "eager",
             "step_pipelining": (("phase A (dedup, partition, key send) of batch i+1 beside the rounds of batch i" if sharded
