@@ -19,7 +19,7 @@ const Knob kKnobs[EDL_TUNE_COUNT] = {
     /* EDL_TUNE_LONG_THR      */ {"long_thr", "EDL_LONG_THR", 16, 2, 1 << 20},
     /* EDL_TUNE_SEG_FORK      */ {"seg_fork", "EDL_SEG_FORK", 1, 0, 1},
     /* EDL_TUNE_DIRECT_BATCH  */ {"direct_batch", "EDL_DIRECT_BATCH", 2, 1, 2},
-    /* EDL_TUNE_SEG_IMPL      */ {"seg_impl", "EDL_SEG_IMPL", 0, 0, 1},
+    /* EDL_TUNE_SEG_IMPL      */ {"seg_impl", "EDL_SEG_IMPL", 2, 0, 2},
     /* EDL_TUNE_STREAM_CTAS   */ {"stream_ctas", "EDL_STREAM_CTAS", 3, 1, 8},
     /* EDL_TUNE_GATHER_IMPL   */ {"gather_impl", "EDL_GATHER_IMPL", 1, 0, 1},
     /* EDL_TUNE_CLASSIFY_SIDE */ {"classify_side", "EDL_CLASSIFY_SIDE", 1, 0, 1},

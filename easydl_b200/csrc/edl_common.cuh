@@ -20,7 +20,7 @@ enum EdlTune {
   EDL_TUNE_LONG_THR = 0,   // ids with more gradient rows than this go through the chunk kernels
   EDL_TUNE_SEG_FORK,       // 1: hot-id kernels on the helper stream beside the main reduce kernel
   EDL_TUNE_DIRECT_BATCH,   // k_seg_direct: ids per lane group (1 or 2)
-  EDL_TUNE_SEG_IMPL,       // 0: k_seg_direct (register path), 1: k_seg_stream (cp.async ring)
+  EDL_TUNE_SEG_IMPL,       // 0: k_seg_direct (register path), 1: k_seg_stream (cp.async ring), 2: by gradient row type and width
   EDL_TUNE_STREAM_CTAS,    // k_seg_stream: persistent CTAs per SM
   EDL_TUNE_GATHER_IMPL,    // 0: k_gather, 1: k_gather_pf (row index of the next iteration prefetched)
   EDL_TUNE_CLASSIFY_SIDE,  // forked update: 1 = k_seg_classify on the helper stream too

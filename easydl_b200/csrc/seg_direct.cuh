@@ -351,7 +351,7 @@ k_seg_long_final(int D4, const int32_t* __restrict__ counters, const int32_t* __
 }
 
 // One call = memset of the counters (update.cu), then
-//   main kernel   k_seg_stream (seg_impl 1, default) or k_seg_direct (0): ids with <= long_thr rows
+//   main kernel   k_seg_direct (seg_impl 0) or k_seg_stream (1), chosen by row type and width (2): ids with <= long_thr rows
 //   hot ids       k_seg_classify -> k_seg_chunk -> k_seg_long_final
 // seg_fork 1 (default): the hot-id branch runs on the device's helper stream beside the main kernel
 // (classify_side 1: from k_seg_classify on, so nothing precedes the main kernel on `st`).
@@ -364,7 +364,11 @@ int launch_direct(const void* grad, const void* grad32, int D4, const int32_t* o
   const int long_thr = std::max(kLongThrMin, edl_tune(EDL_TUNE_LONG_THR));
   const int batch = edl_tune(EDL_TUNE_DIRECT_BATCH);
   const int fork = edl_tune(EDL_TUNE_SEG_FORK);
-  const int impl = edl_tune(EDL_TUNE_SEG_IMPL);
+  // seg_impl 2 (default): the register path for fp32 gradient rows of fewer than 128 floats; the streamed
+  // kernel for float64 / mixed rows (the owner side of the sharded step) and for rows of 512 bytes and more,
+  // where the register path holds too few bytes in flight per warp (dim 256: 997 -> 787 us, r2_experiments 7)
+  int impl = edl_tune(EDL_TUNE_SEG_IMPL);
+  if (impl == 2) impl = (std::is_same<GT, float>::value && D4 < 32) ? 0 : 1;
   const bool cls_side = fork && edl_tune(EDL_TUNE_CLASSIFY_SIDE);
   const bool classify = fork || impl == 1;   // k_seg_direct can list the hot ids itself (unforked launch)
   std::unique_lock<std::mutex> lock(fork_mutex(), std::defer_lock);
