@@ -25,6 +25,8 @@ enum EdlTune {
   EDL_TUNE_GATHER_IMPL,    // 0: k_gather, 1: k_gather_pf (row index of the next iteration prefetched)
   EDL_TUNE_CLASSIFY_SIDE,  // forked update: 1 = k_seg_classify on the helper stream too
   EDL_TUNE_STREAM_STAGES,  // k_seg_stream: ring slots in use (2..4)
+  EDL_TUNE_DEDUP_IMPL,     // field-major dedup: 2 = one cluster sorts one field in shared memory and writes the
+                           // unique outputs, 1 = that sort + separate unique kernels, 0 = global passes
   EDL_TUNE_COUNT
 };
 int edl_tune(int id);

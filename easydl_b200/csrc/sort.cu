@@ -8,9 +8,15 @@
 // Stability inside a tile comes from warp-striped ranking with __match_any_sync: warp w owns
 // 256 consecutive elements, iteration k ranks elements w*256 + k*32 + lane, so rank order ==
 // input order.  Everything for a cfg2 batch (1.7M keys, 28 bits) stays L2-resident.
+#include <cooperative_groups.h>
+
 #include <algorithm>
+#include <mutex>
+#include <type_traits>
 
 #include "edl_common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -263,6 +269,350 @@ k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
   }
 }
 
+// ------------------------------------------------------------------ field sort inside one cluster
+// Field-major batches whose fields hold at most 65536 samples: the whole LSD sort of ONE field runs
+// inside ONE thread-block cluster, the field's (key, sample) pairs never leaving shared memory between
+// the passes.  CTA r of the cluster holds positions [r * chunk, (r + 1) * chunk) of the field in two
+// ping-pong buffers; a pass ranks its elements like k_scatter does (warp-striped, stable), publishes its
+// 256-bin histogram, reads the other CTAs' histograms through distributed shared memory, and stores every
+// element straight into the shared memory of the CTA that owns its destination.  One launch replaces the
+// 3 x (histogram, row scan, scatter) launches of the global path, and (when the tiles line up) the head
+// count of the unique step as well.
+constexpr int kCS = 4;                       // CTAs per cluster (= per field)
+constexpr int kCT = 1024;                    // threads per CTA
+constexpr int kCW = kCT / 32;
+constexpr int kCIter = 16;                   // 32-element rounds per warp and pass, at most
+constexpr int kCCap = kCW * 32 * kCIter;     // 16384 positions per CTA -> 65536 samples per field
+
+static inline size_t cluster_sort_smem(int chunk) {
+  return (size_t)chunk * 12 + (size_t)kCW * 256 * 2 + 256 * 4 * 3 + 64 + 64;
+}
+
+// What the fused form of k_cluster_sort writes besides `order` (the whole unique step).
+struct FusedUnique {
+  int on;
+  int64_t* uniq; int32_t* seg_offsets; int32_t* seg_first; int32_t* inverse; int32_t* n_unique;
+  const int64_t* field_base;
+  unsigned* ticket;                 // zeroed before the launch: fields are handed out in arrival order
+  unsigned long long* field_heads;  // [F], zeroed: (1 << 32) | distinct ids of the field, once known
+};
+
+// ids [B, F] int64 -> keys [F, B] uint32, both sides in whole lines through a shared-memory tile.  Read straight
+// from the id matrix, the ids of one field are 8 bytes out of every F * 8: one sector per id, and the sort
+// kernel's load phase was bound by outstanding sectors (ncu: a quarter of its samples).
+constexpr int kTS = 128;            // samples per CTA
+__global__ void __launch_bounds__(256)
+k_field_major_keys(const int64_t* __restrict__ ids, int F, int B, uint32_t* __restrict__ keys) {
+  extern __shared__ uint32_t tile[];   // [F][kTS + 1]
+  const int b0 = (int)blockIdx.x * kTS;
+  const int nb = min(kTS, B - b0);
+  const int64_t* src = ids + (int64_t)b0 * F;
+  const int total = nb * F;
+  for (int i = threadIdx.x; i < total; i += 256) {
+    const int b = i / F, f = i - b * F;
+    tile[f * (kTS + 1) + b] = (uint32_t)src[i];
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < F * kTS; i += 256) {
+    const int f = i / kTS, b = i % kTS;
+    if (b < nb) keys[(int64_t)f * B + b0 + b] = tile[f * (kTS + 1) + b];
+  }
+}
+
+__global__ void __cluster_dims__(kCS, 1, 1) __launch_bounds__(kCT, 1)
+k_cluster_sort(const int64_t* __restrict__ ids, const uint32_t* __restrict__ keys_fm, int F, int B, int chunk,
+               int passes, uint32_t* __restrict__ keys_out, int32_t* __restrict__ order,
+               uint32_t* __restrict__ tile_heads, FusedUnique fu) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ unsigned s_misc[4];    // [0] field of this cluster (rank 0's copy), [1] heads of this CTA, [2] ids before this field
+  __shared__ unsigned s_wsum[kCW];
+  cg::cluster_group cluster = cg::this_cluster();
+  const int r = (int)cluster.block_rank();
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  int f = (int)blockIdx.x / kCS;
+  if (fu.on) {
+    // Fields in ARRIVAL order: a cluster waits (below) only for clusters that took their ticket before it did,
+    // and those are running.
+    if (r == 0 && tid == 0) s_misc[0] = atomicAdd(fu.ticket, 1u);
+    cluster.sync();
+    f = (int)*cluster.map_shared_rank(&s_misc[0], 0);
+  }
+  uint32_t* kbuf0 = (uint32_t*)smem_raw;
+  uint32_t* kbuf1 = kbuf0 + chunk;
+  uint16_t* vbuf0 = (uint16_t*)(kbuf1 + chunk);
+  uint16_t* vbuf1 = vbuf0 + chunk;
+  uint16_t* cnt = vbuf1 + chunk;                       // [kCW][256]
+  uint32_t* hist = (uint32_t*)(cnt + kCW * 256);       // [256], read by the other CTAs
+  uint32_t* base = hist + 256;                         // [256]
+  uint32_t* lstart = base + 256;                       // [256]
+  uint32_t* warp_sum = lstart + 256;                   // [8] (+ pad)
+  uint32_t* tile_cnt = warp_sum + 16;                  // [8] (+ pad)
+  const int iters = chunk / (kCW * 32);
+  const int p0 = r * chunk;                            // first field position this CTA holds
+
+  {                        // the field's ids of this CTA's positions: every load of a thread in flight at once
+    long long raw[kCIter];
+#pragma unroll
+    for (int k = 0; k < kCIter; ++k) {
+      const int p = p0 + k * kCT + tid;
+      raw[k] = 0ll;
+      if (k < iters && p < B) raw[k] = keys_fm ? (long long)keys_fm[(int64_t)f * B + p] : ids[(int64_t)p * F + f];
+    }
+#pragma unroll
+    for (int k = 0; k < kCIter; ++k) {
+      const int e = k * kCT + tid;
+      if (k < iters && p0 + e < B) {
+        kbuf0[e] = (uint32_t)raw[k];
+        vbuf0[e] = (uint16_t)(p0 + e);
+      }
+    }
+  }
+  if (tid < 8) tile_cnt[tid] = 0;
+  __syncthreads();
+
+  const unsigned lt = edl_lanemask_lt();
+  const int n_local = min(max(B - p0, 0), chunk);      // valid positions of this CTA (a prefix)
+  for (int pass = 0; pass < passes; ++pass) {
+    // Every pass: kbuf0 / vbuf0 -> (ranked, grouped by digit) kbuf1 / vbuf1 of THIS CTA -> kbuf0 / vbuf0 of the
+    // CTAs that own the destinations.  Grouping locally first makes the stores into the other CTAs' shared
+    // memory run over consecutive addresses (scattered 4-byte remote stores took 3x the time of the rest).
+    const int shift = pass * 8;
+    uint16_t* wc = cnt + w * 256;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) wc[i * 32 + lane] = 0;
+    __syncwarp();
+    // Lanes with my digit, from eight ballots instead of __match_any_sync: MATCH.ANY walks the distinct values of
+    // the warp one by one (ncu: one warp-wide match per ~30 cycles and SM, the largest share of this kernel),
+    // and the sixteen rounds of a pass are independent until the counters are touched.
+    unsigned dr[kCIter];   // peers, then: digit in bits 0..8 (256 = no element), rank inside the warp's run above
+    unsigned dg[kCIter];
+#pragma unroll
+    for (int k = 0; k < kCIter; ++k) {
+      dr[k] = 0u;
+      dg[k] = 256u;
+      if (k < iters) {
+        const int e = w * (iters * 32) + k * 32 + lane;
+        const bool valid = e < n_local;
+        const unsigned d = valid ? ((kbuf0[e] >> shift) & 0xFFu) : 256u;
+        unsigned peers = __ballot_sync(0xffffffffu, valid);
+        if (!valid) peers = ~peers;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+          const unsigned bal = __ballot_sync(0xffffffffu, (d >> b) & 1u);
+          peers &= ((d >> b) & 1u) ? bal : ~bal;
+        }
+        dr[k] = peers;
+        dg[k] = d;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kCIter; ++k) {
+      if (k < iters) {
+        const unsigned d = dg[k], mask = dr[k];
+        const bool valid = d < 256u;
+        const int leader = __ffs(mask) - 1;
+        unsigned prev = 0;
+        if (lane == leader && valid) prev = wc[d];
+        prev = __shfl_sync(0xffffffffu, prev, leader);
+        dr[k] = d | ((prev + __popc(mask & lt)) << 9);
+        if (lane == leader && valid) wc[d] = (uint16_t)(prev + __popc(mask));
+        __syncwarp();
+      } else {
+        dr[k] = 256u;
+      }
+    }
+    __syncthreads();
+    unsigned mine = 0;
+    if (tid < 256) {       // this CTA's histogram; the warps' counts become their offsets inside the digit
+      unsigned run = 0;
+#pragma unroll 8
+      for (int i = 0; i < kCW; ++i) {
+        const unsigned c = cnt[i * 256 + tid];
+        cnt[i * 256 + tid] = (uint16_t)run;
+        run += c;
+      }
+      hist[tid] = run;
+      mine = run;
+    }
+    {                      // where each digit starts inside this CTA: exclusive scan of its histogram
+      unsigned inc = mine;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+      }
+      if (tid < 256 && lane == 31) warp_sum[w] = inc;
+      __syncthreads();
+      if (tid < 256) {
+        unsigned wbase = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (i < w) wbase += warp_sum[i];
+        lstart[tid] = wbase + inc - mine;
+      }
+      __syncthreads();
+    }
+#pragma unroll
+    for (int k = 0; k < kCIter; ++k) {
+      const unsigned d = dr[k] & 511u;
+      if (k < iters && d < 256u) {
+        const int e = w * (iters * 32) + k * 32 + lane;
+        const unsigned q = lstart[d] + wc[d] + (dr[k] >> 9);
+        kbuf1[q] = kbuf0[e];
+        vbuf1[q] = vbuf0[e];
+      }
+    }
+    cluster.sync();        // histograms published, every CTA has left its kbuf0 / vbuf0 (and is running)
+    unsigned total = 0, below = 0;
+    if (tid < 256) {
+#pragma unroll
+      for (int rr = 0; rr < kCS; ++rr) {
+        const uint32_t* h = cluster.map_shared_rank(hist, rr);
+        const unsigned v = h[tid];
+        total += v;
+        if (rr < r) below += v;
+      }
+    }
+    unsigned inc = total;  // exclusive scan of the 256 digit totals (warps 0..7)
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned v = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += v;
+    }
+    if (tid < 256 && lane == 31) warp_sum[w] = inc;
+    __syncthreads();
+    if (tid < 256) {
+      unsigned wbase = 0;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (i < w) wbase += warp_sum[i];
+      // position inside the field of this CTA's first element with digit `tid`, minus where that element sits here
+      base[tid] = wbase + inc - total + below - lstart[tid];
+    }
+    __syncthreads();
+    for (int q = tid; q < n_local; q += kCT) {
+      const uint32_t key = kbuf1[q];
+      const unsigned p = base[(key >> shift) & 0xFFu] + (unsigned)q;
+      const unsigned rr = (p >= (unsigned)chunk) + (p >= 2u * chunk) + (p >= 3u * chunk);
+      const unsigned off = p - rr * chunk;
+      cluster.map_shared_rank(kbuf0, rr)[off] = key;
+      cluster.map_shared_rank(vbuf0, rr)[off] = vbuf1[q];
+    }
+    cluster.sync();        // all stores of the pass have landed; kbuf1 / vbuf1 may be overwritten
+  }
+
+  const uint32_t* kf = kbuf0;
+  const uint16_t* vf = vbuf0;
+  uint32_t prevb = 0;      // the key in front of this CTA's first position
+  if (r > 0 && p0 < B) prevb = cluster.map_shared_rank(kf, r - 1)[chunk - 1];
+
+  if (fu.on) {
+    // The unique step in place: head flags as one ballot per round, heads counted over warp -> CTA -> cluster ->
+    // the fields in front (their totals are published in field_heads as soon as they are known), then uniq /
+    // seg_offsets / seg_first / inverse / order are written from shared memory.
+    unsigned hb[kCIter];
+    unsigned wtot = 0;
+#pragma unroll
+    for (int k = 0; k < kCIter; ++k) {
+      hb[k] = 0u;
+      if (k < iters) {
+        const int e = w * (iters * 32) + k * 32 + lane;
+        bool head = false;
+        if (e < n_local) head = (p0 + e == 0) || kf[e] != (e > 0 ? kf[e - 1] : prevb);
+        hb[k] = __ballot_sync(0xffffffffu, head);
+        wtot += __popc(hb[k]);
+      }
+    }
+    if (lane == 0) s_wsum[w] = wtot;
+    __syncthreads();
+    if (w == 0) {
+      const unsigned v = s_wsum[lane];
+      unsigned inc = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned x = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += x;
+      }
+      s_wsum[lane] = inc - v;
+      if (lane == 31) s_misc[1] = inc;
+    }
+    cluster.sync();        // every CTA's head count is known
+    unsigned below = 0, field_total = 0;
+#pragma unroll
+    for (int rr = 0; rr < kCS; ++rr) {
+      const unsigned v = *cluster.map_shared_rank(&s_misc[1], rr);
+      field_total += v;
+      if (rr < r) below += v;
+    }
+    if (r == 0 && tid == 0)
+      atomicExch(fu.field_heads + f, (1ull << 32) | (unsigned long long)field_total);
+    if (w == 0) {          // distinct ids of the fields in front of this one
+      unsigned sum = 0;
+      for (int j = lane; j < f; j += 32) {
+        unsigned long long v;
+        do { v = *(volatile unsigned long long*)(fu.field_heads + j); } while ((v >> 32) == 0ull);
+        sum += (unsigned)v;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+      if (lane == 0) s_misc[2] = sum;
+    }
+    __syncthreads();
+    const unsigned before = s_misc[2];
+    unsigned run = before + below + s_wsum[w];
+    const long long fbase = fu.field_base[f];
+    const unsigned le = lt | (1u << lane);
+#pragma unroll
+    for (int k = 0; k < kCIter; ++k) {
+      if (k < iters) {
+        const int e = w * (iters * 32) + k * 32 + lane;
+        if (e < n_local) {
+          const unsigned u = run + __popc(hb[k] & le) - 1u;
+          const int64_t i = (int64_t)f * B + p0 + e;
+          const int32_t pos = (int32_t)((uint32_t)vf[e] * (uint32_t)F + (uint32_t)f);
+          order[i] = pos;
+          if (fu.inverse) fu.inverse[pos] = (int32_t)u;
+          if ((hb[k] >> lane) & 1u) {
+            fu.uniq[u] = (int64_t)kf[e] + fbase;
+            fu.seg_offsets[u] = (int32_t)i;
+            if (fu.seg_first) fu.seg_first[u] = pos;
+          }
+        }
+        run += __popc(hb[k]);
+      }
+    }
+    if (f == F - 1 && r == 0 && tid == 0) {
+      const unsigned U = before + field_total;
+      *fu.n_unique = (int32_t)U;
+      fu.seg_offsets[U] = (int32_t)((int64_t)F * B);
+    }
+    cluster.sync();        // no CTA leaves while its neighbours may still read its last key / head count
+    return;
+  }
+
+  for (int e = tid; e < chunk; e += kCT) {
+    const int p = p0 + e;
+    unsigned c = 0;
+    if (p < B) {
+      const uint32_t key = kf[e];
+      const uint32_t pv = e > 0 ? kf[e - 1] : prevb;
+      const int64_t i = (int64_t)f * B + p;
+      keys_out[i] = key;
+      order[i] = (int32_t)((uint32_t)vf[e] * (uint32_t)F + (uint32_t)f);
+      c = (p == 0 || key != pv) ? 1u : 0u;
+    }
+    if (tile_heads) {      // chunk and B are multiples of the 2048-element tiles of the unique kernels
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+      if (lane == 0 && c) atomicAdd(&tile_cnt[e >> 11], c);
+    }
+  }
+  __syncthreads();
+  if (tile_heads && tid < (chunk >> 11) && p0 + tid * 2048 < B)
+    tile_heads[((int64_t)f * B + p0 + tid * 2048) >> 11] = tile_cnt[tid];
+  cluster.sync();          // no CTA leaves while its neighbour may still read its last key
+}
+
 // ------------------------------------------------------------------ unique kernels
 template <typename KeyT>
 __global__ void __launch_bounds__(kThreads)
@@ -417,14 +767,17 @@ struct UniqueWs {
 // Field-major mode (fused [B, F] batches): sort every field's ids separately on their own
 // `field_bits` instead of the fused key's `key_bits` -- the field is known from the position, so
 // its bits need no radix pass (cfg2: 24 instead of 28 bits = 3 passes instead of 4).
-struct FmPlan { bool on; int F; int64_t B, Bp; int tpf; };
+struct FmPlan { bool on; int F; int64_t B, Bp; int tpf; bool in_cluster; };
 
 FmPlan fm_plan(int64_t n, const int32_t* n_dev, const int64_t* field_base, int n_fields, int key_bits,
                int field_bits) {
-  FmPlan f{false, 1, n, n, 0};
+  FmPlan f{false, 1, n, n, 0, false};
   if (field_bits <= 0 || !field_base || n_fields <= 1 || n_dev || n % n_fields != 0) return f;
-  if ((field_bits + 7) / 8 >= (key_bits + 7) / 8) return f;   // no pass saved
+  // worth it when a radix pass is saved, or when the fields are small enough for k_cluster_sort
+  const bool in_cluster = field_bits <= 32 && n / n_fields <= (int64_t)kCS * kCCap && edl_tune(EDL_TUNE_DEDUP_IMPL) >= 1;
+  if ((field_bits + 7) / 8 >= (key_bits + 7) / 8 && !in_cluster) return f;
   f.on = true;
+  f.in_cluster = in_cluster;
   f.F = n_fields;
   f.B = n / n_fields;
   f.tpf = (int)edl_cdiv(f.B, kTile);
@@ -467,6 +820,22 @@ void rowscan(uint32_t* hist, int n_tiles, uint32_t* tot, int tps, int n_seg, cud
     k_rowscan<<<256 * n_seg, kThreads, 0, st>>>(hist, n_tiles, tot, tps);
 }
 
+// k_cluster_sort needs more dynamic shared memory than the default limit: raised once per device.
+int cluster_sort_prepare() {
+  static std::mutex mu;
+  static bool done[64] = {false};
+  int dev = -1;
+  EDL_CUDA(cudaGetDevice(&dev));
+  EDL_REQUIRE(dev >= 0 && dev < 64, EDL_ELIMIT, "edl_unique: device ordinal %d beyond 64", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!done[dev]) {
+    EDL_CUDA(cudaFuncSetAttribute(k_cluster_sort, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)cluster_sort_smem(kCCap)));
+    done[dev] = true;
+  }
+  return EDL_OK;
+}
+
 template <typename KeyT>
 int unique_impl(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64_t* field_base,
                 int n_fields, int key_bits, int field_bits, int64_t* uniq, int32_t* inverse,
@@ -482,7 +851,47 @@ int unique_impl(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64
     vbuf[(passes - 1) & 1] = (uint32_t*)order;
     vbuf[passes & 1] = W.valsB;
   }
-  for (int p = 0; p < passes; ++p) {
+  const KeyT* sorted = kbuf[(passes - 1) & 1];
+  bool heads_done = false;
+  bool in_cluster = false;
+  if constexpr (std::is_same<KeyT, uint32_t>::value) {
+    if (fm.on && fm.in_cluster) {
+      const int chunk = (int)(edl_cdiv(edl_cdiv(fm.B, kCS), kCW * 32) * (kCW * 32));
+      const size_t smem = cluster_sort_smem(chunk);
+      int rc = cluster_sort_prepare();
+      if (rc) return rc;
+      const int mode = edl_tune(EDL_TUNE_DEDUP_IMPL);
+      // ids -> field-major 32-bit keys first (in the second key buffer, which this path does not use otherwise)
+      const uint32_t* keys_fm = nullptr;
+      const size_t tile_bytes = (size_t)fm.F * (kTS + 1) * 4;
+      if (tile_bytes <= 48 * 1024) {
+        k_field_major_keys<<<(unsigned)edl_cdiv(fm.B, kTS), 256, tile_bytes, st>>>(ids, fm.F, (int)fm.B, (uint32_t*)kbuf[1]);
+        keys_fm = (const uint32_t*)kbuf[1];
+      }
+      FusedUnique fu{};
+      if (mode == 2) {     // the unique step inside the sort kernel: ticket + per-field totals start at zero
+        const size_t sync_bytes = 8 + 8 * (size_t)fm.F;
+        EDL_CUDA(cudaMemsetAsync(W.tot, 0, sync_bytes, st));
+        fu = FusedUnique{1, uniq, seg_offsets, seg_first, inverse, n_unique, field_base, (unsigned*)W.tot,
+                         (unsigned long long*)(W.tot + 2)};
+      }
+      heads_done = !fu.on && fm.B % kTile == 0 && chunk % kTile == 0;
+      k_cluster_sort<<<fm.F * kCS, kCT, smem, st>>>(ids, keys_fm, fm.F, (int)fm.B, chunk, passes, (uint32_t*)kbuf[0],
+                                                    order, heads_done ? W.tile_heads : (uint32_t*)nullptr, fu);
+      EDL_LAUNCH_CHECK("k_cluster_sort");
+      if (fu.on) {
+        if (counts) {
+          int g = (int)std::min<int64_t>(edl_cdiv(n, 256), EDL_SM_COUNT * 8);
+          k_counts<<<g, 256, 0, st>>>(seg_offsets, n_unique, counts);
+          EDL_LAUNCH_CHECK("k_counts");
+        }
+        return EDL_OK;
+      }
+      sorted = kbuf[0];
+      in_cluster = true;
+    }
+  }
+  for (int p = 0; p < passes && !in_cluster; ++p) {
     const bool last = p == passes - 1;
     BitDigit<KeyT> dg{p * 8};
     KeyT* ko = kbuf[p & 1];
@@ -511,9 +920,8 @@ int unique_impl(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64
   }
   EDL_LAUNCH_CHECK("radix passes");
   const int tiles = (int)edl_cdiv(n, kTile);
-  const KeyT* sorted = kbuf[(passes - 1) & 1];
   const int64_t seg_len = fm.on ? fm.B : 0;
-  k_head_count<KeyT><<<tiles, kThreads, 0, st>>>(sorted, n, n_dev, W.tile_heads, seg_len);
+  if (!heads_done) k_head_count<KeyT><<<tiles, kThreads, 0, st>>>(sorted, n, n_dev, W.tile_heads, seg_len);
   k_scan_tiles<<<1, 1024, 0, st>>>(W.tile_heads, tiles, n, n_dev, n_unique, seg_offsets);
   k_unique_write<KeyT><<<tiles, kThreads, 0, st>>>(sorted, (const uint32_t*)order, n, n_dev, W.tile_heads, uniq,
                                                    seg_offsets, seg_first, inverse, seg_len, field_base);
@@ -630,7 +1038,6 @@ extern "C" int edl_partition_mod(const int64_t* keys, int64_t n, const int32_t* 
 // CUDA runtime understands -- it is not a device address and must never be handed to a kernel
 // as a pointer.  The real address is asked for once per device with cudaGetSymbolAddress
 // (with that device current) and cached in g_static_addr[].
-#include <mutex>
 
 static __device__ __align__(256) unsigned char g_unique_scratch[EDL_UNIQUE_STATIC_SCRATCH_BYTES];
 
@@ -685,9 +1092,9 @@ extern "C" int edl_unique_static(const int64_t* ids, int64_t n, const int32_t* n
   EDL_REQUIRE(W.bytes <= (size_t)EDL_UNIQUE_STATIC_SCRATCH_BYTES, EDL_ELIMIT,
               "edl_unique_static: n=%lld at key_bits=%d needs %zu scratch bytes, the built-in array has %d",
               (long long)n, key_bits, W.bytes, EDL_UNIQUE_STATIC_SCRATCH_BYTES);
-  // Nothing in the scratch has to start at zero: every histogram cell, digit total and tile
-  // count is written by this call before this call reads it, so whatever the previous call
-  // left behind is never observed.
+  // Nothing in the scratch has to be zero when this call starts: every histogram cell, digit total
+  // and tile count is written by this call before this call reads it, and the few words the fused
+  // sort kernel needs at zero (its ticket and per-field totals) are cleared by this call on `stream`.
   if (sort_keys_32(n, n_dev, field_base, n_fields, key_bits, field_bits))
     return unique_impl<uint32_t>(ids, n, n_dev, field_base, n_fields, key_bits, field_bits, uniq, inverse, counts,
                                  order, seg_offsets, seg_first, n_unique, W, st);

@@ -74,6 +74,10 @@ const char* edl_last_error_string(void);
  *   stream_stages (EDL_STREAM_STAGES, 4)  k_seg_stream: ring slots in use, 2..4 (bytes in flight per warp)
  *   direct_batch  (EDL_DIRECT_BATCH, 2)   k_seg_direct: ids per lane group
  *   gather_impl   (EDL_GATHER_IMPL, 1)    gather kernels: 1 = next iteration's row index prefetched
+ *   dedup_impl    (EDL_DEDUP_IMPL, 2)     edl_unique on field-major batches of at most 65536 samples: 2 = every
+ *                                         field sorted by one thread-block cluster in shared memory, which also
+ *                                         writes the unique step's outputs; 1 = the same sort, unique step as
+ *                                         separate kernels; 0 = the global counting-sort passes
  * Unknown names and out-of-range values return EDL_EINVAL. */
 int edl_tuning_set(const char* name, int value);
 int edl_tuning_get(const char* name, int* value_out);
