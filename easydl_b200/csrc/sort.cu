@@ -285,7 +285,7 @@ constexpr int kCIter = 16;                   // 32-element rounds per warp and p
 constexpr int kCCap = kCW * 32 * kCIter;     // 16384 positions per CTA -> 65536 samples per field
 
 static inline size_t cluster_sort_smem(int chunk) {
-  return (size_t)chunk * 12 + (size_t)kCW * 256 * 2 + 256 * 4 * 3 + 64 + 64;
+  return (size_t)chunk * 12 + (size_t)kCW * 256 * 2 + 256 * 4 * 3 + 64 + 64 + ((size_t)chunk * 4 >= kCW * 2048 ? 0 : kCW * 2048);
 }
 
 // What the fused form of k_cluster_sort writes besides `order` (the whole unique step).
@@ -347,6 +347,8 @@ k_cluster_sort(const int64_t* __restrict__ ids, const uint32_t* __restrict__ key
   uint32_t* lstart = base + 256;                       // [256]
   uint32_t* warp_sum = lstart + 256;                   // [8] (+ pad)
   uint32_t* tile_cnt = warp_sum + 16;                  // [8] (+ pad)
+  // [kCW][2][256] peer-mask words of the ranking: in kbuf1 when that is large enough, else behind everything
+  uint32_t* mm_base = chunk * 4 >= kCW * 2048 ? kbuf1 : tile_cnt + 16;
   const int iters = chunk / (kCW * 32);
   const int p0 = r * chunk;                            // first field position this CTA holds
 
@@ -372,6 +374,12 @@ k_cluster_sort(const int64_t* __restrict__ ids, const uint32_t* __restrict__ key
 
   const unsigned lt = edl_lanemask_lt();
   const int n_local = min(max(B - p0, 0), chunk);      // valid positions of this CTA (a prefix)
+  unsigned krem[kCS], vrem[kCS];                       // kbuf0 / vbuf0 of every CTA of the cluster (shared::cluster window)
+#pragma unroll
+  for (int rr = 0; rr < kCS; ++rr) {
+    asm("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(krem[rr]) : "r"((unsigned)__cvta_generic_to_shared(kbuf0)), "r"(rr));
+    asm("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(vrem[rr]) : "r"((unsigned)__cvta_generic_to_shared(vbuf0)), "r"(rr));
+  }
   for (int pass = 0; pass < passes; ++pass) {
     // Every pass: kbuf0 / vbuf0 -> (ranked, grouped by digit) kbuf1 / vbuf1 of THIS CTA -> kbuf0 / vbuf0 of the
     // CTAs that own the destinations.  Grouping locally first makes the stores into the other CTAs' shared
@@ -381,44 +389,37 @@ k_cluster_sort(const int64_t* __restrict__ ids, const uint32_t* __restrict__ key
 #pragma unroll
     for (int i = 0; i < 8; ++i) wc[i * 32 + lane] = 0;
     __syncwarp();
-    // Lanes with my digit, from eight ballots instead of __match_any_sync: MATCH.ANY walks the distinct values of
-    // the warp one by one (ncu: one warp-wide match per ~30 cycles and SM, the largest share of this kernel),
-    // and the sixteen rounds of a pass are independent until the counters are touched.
-    unsigned dr[kCIter];   // peers, then: digit in bits 0..8 (256 = no element), rank inside the warp's run above
-    unsigned dg[kCIter];
+    // Lanes with my digit: every lane ORs its bit into the digit's word of a per-warp table and reads the word
+    // back (8 ballots per round cost 90 instructions, MATCH.ANY walks the warp's distinct values one by one: ncu
+    // had either at a third of this kernel).  Two tables in turn, so that the leader's clearing of one round's
+    // words cannot meet the next round's ORs.  The tables live in the grouping buffer, idle at this point.
+    uint32_t* mm = mm_base + w * 512;
+    {
+      const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) ((uint4*)mm)[i * 32 + lane] = z;
+    }
+    __syncwarp();
+    unsigned dr[kCIter];   // digit in bits 0..8 (256 = no element), rank inside the warp's run of the digit above
 #pragma unroll
     for (int k = 0; k < kCIter; ++k) {
-      dr[k] = 0u;
-      dg[k] = 256u;
+      dr[k] = 256u;
       if (k < iters) {
         const int e = w * (iters * 32) + k * 32 + lane;
         const bool valid = e < n_local;
         const unsigned d = valid ? ((kbuf0[e] >> shift) & 0xFFu) : 256u;
-        unsigned peers = __ballot_sync(0xffffffffu, valid);
-        if (!valid) peers = ~peers;
-#pragma unroll
-        for (int b = 0; b < 8; ++b) {
-          const unsigned bal = __ballot_sync(0xffffffffu, (d >> b) & 1u);
-          peers &= ((d >> b) & 1u) ? bal : ~bal;
-        }
-        dr[k] = peers;
-        dg[k] = d;
-      }
-    }
-#pragma unroll
-    for (int k = 0; k < kCIter; ++k) {
-      if (k < iters) {
-        const unsigned d = dg[k], mask = dr[k];
-        const bool valid = d < 256u;
-        const int leader = __ffs(mask) - 1;
-        unsigned prev = 0;
-        if (lane == leader && valid) prev = wc[d];
-        prev = __shfl_sync(0xffffffffu, prev, leader);
-        dr[k] = d | ((prev + __popc(mask & lt)) << 9);
-        if (lane == leader && valid) wc[d] = (uint16_t)(prev + __popc(mask));
+        uint32_t* m = mm + (k & 1) * 256;
+        if (valid) atomicOr(m + d, 1u << lane);
         __syncwarp();
-      } else {
-        dr[k] = 256u;
+        unsigned peers = 0, prev = 0;
+        if (valid) { peers = m[d]; prev = wc[d]; }
+        __syncwarp();
+        const unsigned below = __popc(peers & lt);
+        if (valid && below == 0) {          // first lane of the digit: next round's count, word back to zero
+          m[d] = 0u;
+          wc[d] = (uint16_t)(prev + __popc(peers));
+        }
+        dr[k] = d | ((prev + below) << 9);
       }
     }
     __syncthreads();
@@ -490,13 +491,32 @@ k_cluster_sort(const int64_t* __restrict__ ids, const uint32_t* __restrict__ key
       base[tid] = wbase + inc - total + below - lstart[tid];
     }
     __syncthreads();
-    for (int q = tid; q < n_local; q += kCT) {
-      const uint32_t key = kbuf1[q];
-      const unsigned p = base[(key >> shift) & 0xFFu] + (unsigned)q;
-      const unsigned rr = (p >= (unsigned)chunk) + (p >= 2u * chunk) + (p >= 3u * chunk);
-      const unsigned off = p - rr * chunk;
-      cluster.map_shared_rank(kbuf0, rr)[off] = key;
-      cluster.map_shared_rank(vbuf0, rr)[off] = vbuf1[q];
+#pragma unroll
+    for (int h = 0; h < kCIter; h += 8) {    // eight elements per thread in flight
+      uint32_t ck[8], cp[8];
+      uint16_t cv[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int q = (h + k) * kCT + tid;
+        if (h + k < iters && q < n_local) {
+          ck[k] = kbuf1[q];
+          cv[k] = vbuf1[q];
+          cp[k] = base[(ck[k] >> shift) & 0xFFu] + (unsigned)q;
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int q = (h + k) * kCT + tid;
+        if (h + k < iters && q < n_local) {
+          const unsigned p = cp[k];
+          const unsigned rr = (p >= (unsigned)chunk) + (p >= 2u * chunk) + (p >= 3u * chunk);
+          const unsigned off = p - rr * chunk;
+          const unsigned ka = rr < 2 ? (rr == 0 ? krem[0] : krem[1]) : (rr == 2 ? krem[2] : krem[3]);
+          const unsigned va = rr < 2 ? (rr == 0 ? vrem[0] : vrem[1]) : (rr == 2 ? vrem[2] : vrem[3]);
+          asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(ka + off * 4u), "r"(ck[k]) : "memory");
+          asm volatile("st.shared::cluster.u16 [%0], %1;" ::"r"(va + off * 2u), "h"(cv[k]) : "memory");
+        }
+      }
     }
     cluster.sync();        // all stores of the pass have landed; kbuf1 / vbuf1 may be overwritten
   }
