@@ -374,7 +374,7 @@ def run_b200_arm(a):
 
     # ---------------- device-resident timed region
     # S == 1, Adagrad: the step is replayed from CUDA graphs (one per id batch buffer), which
-    # removes the host launch gaps between its 17 kernels.  Otherwise: eager launches.
+    # removes the host launch gaps between its kernels.  Otherwise: eager launches.
     # unique ids per batch (deterministic per batch buffer): read once, outside the timed region
     U_batch = []
     for i in range(nb):
@@ -624,7 +624,8 @@ def run_b200_arm(a):
             t_lk = phases["lookup_ms"] * 1e-3
             ach = update_b / t_up / 1e9
             line["roofline"] = {
-                "kernel": "k_seg_stream || (k_seg_classify -> k_seg_chunk -> k_seg_long_final) (segmented reduce + "
+                "kernel": ("k_seg_direct" if a.dim < 128 else "k_seg_stream") +
+                          " || (k_seg_classify -> k_seg_chunk -> k_seg_long_final) (segmented reduce + "
                           "row update: four launches per step, hot-id kernels on a forked branch, timed together)",
                 "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": traffic, "traffic_source": traffic_src, "peak_kind": peak_kind,

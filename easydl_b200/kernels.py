@@ -140,6 +140,34 @@ def unique(ids: torch.Tensor, field_base: Optional[torch.Tensor] = None, key_bit
     return out
 
 
+def unique_launches(n: int, n_fields: int, key_bits: int, field_bits: int = 0, *, n_dev: bool = False,
+                    want_counts: bool = False) -> int:
+    """Kernel launches one edl_unique call makes (sort.cu, unique_impl) -- for the launch counts bench.py
+    reports.  Mirrors the path choice there: field-major batches of at most 65536 samples per field go
+    through k_field_major_keys + k_cluster_sort (dedup_impl 1 / 2), everything else through three
+    kernels per 8-bit radix pass plus three unique kernels."""
+    if n == 0:
+        return 1
+    extra = 1 if want_counts else 0
+    passes_flat = (key_bits + 7) // 8
+    fm_ok = field_bits > 0 and n_fields > 1 and not n_dev and n % n_fields == 0
+    if fm_ok:
+        impl = _lib.tuning_get("dedup_impl")
+        B = n // n_fields
+        in_cluster = field_bits <= 32 and B <= 65536 and impl >= 1
+        passes_fm = (field_bits + 7) // 8
+        if in_cluster:
+            transposed = 1 if n_fields * 129 * 4 <= 48 * 1024 else 0
+            if impl == 2:
+                return transposed + 1 + extra
+            chunk = ((B + 3) // 4 + 1023) // 1024 * 1024
+            heads_fused = B % 2048 == 0 and chunk % 2048 == 0
+            return transposed + 1 + (0 if heads_fused else 1) + 2 + extra
+        if passes_fm < passes_flat:
+            return 3 * passes_fm + 3 + extra
+    return 3 * passes_flat + 3 + extra
+
+
 # ------------------------------------------------------------------------------- A2
 @dataclass
 class PartitionResult:

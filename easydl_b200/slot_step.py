@@ -235,11 +235,10 @@ class SlotShardedStep:
         self.side_pf = None
         self._ahead = None
         self.last_n_unique = self.uq.n_unique
-        passes1 = min((self.key_bits + 7) // 8, (self.field_bits + 7) // 8) if self.field_bits else (self.key_bits + 7) // 8
-        passes2 = (self.key_bits + 7) // 8
         # A: unique, partition 4, send 1; B: S gathers; C: positions, compose, expand, 2 torch ops, reduce 4;
         # D: compact, unique, 2 remaps, update 4; 3 fences
-        self.launches_per_step = (3 * passes1 + 3) + 4 + 1 + self.S + 3 + 2 + 4 + 1 + (3 * passes2 + 3) + 2 + 4 + 3
+        self.launches_per_step = (K.unique_launches(N, self.F, self.key_bits, self.field_bits) + 4 + 1 + self.S + 3 + 2 + 4
+                                  + 1 + K.unique_launches(N, 0, self.key_bits, n_dev=True) + 2 + 4 + 3)
 
     # ------------------------------------------------------------------ phases
     def phase_a(self, ids: torch.Tensor, front=None, gen: Optional[int] = None):

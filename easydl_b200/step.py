@@ -47,10 +47,9 @@ class SparseStep:
         self.ws_unique_next = None
         self._ahead = None          # data_ptr of the id batch whose dedup sits in self.uq
         self.ws_seg = torch.empty(lib.edl_segreduce_workspace_bytes(N, N, D), dtype=torch.uint8, device=dev)
-        # launches per step (for bench.py's gpu_launches): gather 1; unique 3/pass + 3; update 4
-        # (k_seg_classify, main kernel, k_seg_chunk, k_seg_long_final) + one memset node
-        passes = min((self.key_bits + 7) // 8, (self.field_bits + 7) // 8)
-        self.launches_per_step = 1 + 3 * passes + 3 + 4
+        # launches per step (for bench.py's gpu_launches): gather 1; unique (K.unique_launches); update 4
+        # (k_seg_classify, main kernel, k_seg_chunk, k_seg_long_final) + memset nodes
+        self.launches_per_step = 1 + K.unique_launches(N, self.F, self.key_bits, self.field_bits) + 4
         self.last_n_unique = self.uq.n_unique
         # The lookup does not need the dedup (it gathers by id), so the two can run side by side:
         # the radix passes are short latency-bound kernels, the gather is one long HBM-bound one.

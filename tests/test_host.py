@@ -232,3 +232,24 @@ def test_restore_skips_incomplete_versions(tmp_path):
         ck.latest_complete_version(d)
     _touch_version(d, 3, range(3), 3)
     assert ck.latest_complete_version(d) == 3
+
+
+def test_unique_launch_count_follows_the_dedup_path():
+    """K.unique_launches mirrors sort.cu's choice of path (bench.py's gpu_launches is built from it)."""
+    from easydl_b200 import _lib
+    from easydl_b200 import kernels as K
+    saved = _lib.tuning_get("dedup_impl")
+    try:
+        _lib.tuning_set("dedup_impl", 2)
+        assert K.unique_launches(65536 * 26, 26, 28, 24) == 2          # transpose + cluster sort (writes everything)
+        assert K.unique_launches(65536 * 26, 26, 28, 24, want_counts=True) == 3
+        assert K.unique_launches(65537 * 26, 26, 28, 24) == 3 * 3 + 3  # field too long: global passes, one saved
+        assert K.unique_launches(1000, 0, 28, n_dev=True) == 4 * 3 + 3
+        _lib.tuning_set("dedup_impl", 1)
+        assert K.unique_launches(65536 * 26, 26, 28, 24) == 4          # + scan + unique write, head count fused
+        assert K.unique_launches(1000 * 26, 26, 28, 24) == 5
+        _lib.tuning_set("dedup_impl", 0)
+        assert K.unique_launches(65536 * 26, 26, 28, 24) == 12
+        assert K.unique_launches(32768 * 26, 26, 30, 26) == 15         # no pass saved: flat sort
+    finally:
+        _lib.tuning_set("dedup_impl", saved)
