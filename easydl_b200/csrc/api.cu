@@ -25,6 +25,7 @@ const Knob kKnobs[EDL_TUNE_COUNT] = {
     /* EDL_TUNE_CLASSIFY_SIDE */ {"classify_side", "EDL_CLASSIFY_SIDE", 1, 0, 1},
     /* EDL_TUNE_STREAM_STAGES */ {"stream_stages", "EDL_STREAM_STAGES", 4, 2, 4},
     /* EDL_TUNE_DEDUP_IMPL    */ {"dedup_impl", "EDL_DEDUP_IMPL", 2, 0, 2},
+    /* EDL_TUNE_DEDUP_SHAPE   */ {"dedup_shape", "EDL_DEDUP_SHAPE", 0, 0, 1},
 };
 std::atomic<int> g_knob[EDL_TUNE_COUNT];
 std::once_flag g_knob_once;

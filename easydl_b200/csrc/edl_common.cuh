@@ -27,6 +27,7 @@ enum EdlTune {
   EDL_TUNE_STREAM_STAGES,  // k_seg_stream: ring slots in use (2..4)
   EDL_TUNE_DEDUP_IMPL,     // field-major dedup: 2 = one cluster sorts one field in shared memory and writes the
                            // unique outputs, 1 = that sort + separate unique kernels, 0 = global passes
+  EDL_TUNE_DEDUP_SHAPE,    // k_cluster_sort: 0 = 4 CTAs x 1024 threads per field, 1 = 8 CTAs x 512 threads
   EDL_TUNE_COUNT
 };
 int edl_tune(int id);

@@ -278,14 +278,14 @@ k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
 // element straight into the shared memory of the CTA that owns its destination.  One launch replaces the
 // 3 x (histogram, row scan, scatter) launches of the global path, and (when the tiles line up) the head
 // count of the unique step as well.
-constexpr int kCS = 4;                       // CTAs per cluster (= per field)
-constexpr int kCT = 1024;                    // threads per CTA
-constexpr int kCW = kCT / 32;
+// Two shapes (template parameters kCS = CTAs per cluster, kCT = threads per CTA; knob dedup_shape):
+//   4 x 1024: 16384 positions and 215 KB of shared memory per CTA, one CTA per SM, the whole register file
+//   8 x 512 :  8192 positions and 107 KB per CTA, half the register file: other kernels' CTAs fit beside it
 constexpr int kCIter = 16;                   // 32-element rounds per warp and pass, at most
-constexpr int kCCap = kCW * 32 * kCIter;     // 16384 positions per CTA -> 65536 samples per field
+constexpr int kClusterMaxField = 65536;      // kCS * (kCT / 32) * 32 * kCIter for both shapes
 
-static inline size_t cluster_sort_smem(int chunk) {
-  return (size_t)chunk * 12 + (size_t)kCW * 256 * 2 + 256 * 4 * 3 + 64 + 64 + ((size_t)chunk * 4 >= kCW * 2048 ? 0 : kCW * 2048);
+static inline size_t cluster_sort_smem(int chunk, int warps) {
+  return (size_t)chunk * 12 + (size_t)warps * 256 * 2 + 256 * 4 * 3 + 64 + 64 + ((size_t)chunk * 4 >= (size_t)warps * 2048 ? 0 : (size_t)warps * 2048);
 }
 
 // What the fused form of k_cluster_sort writes besides `order` (the whole unique step).
@@ -319,13 +319,15 @@ k_field_major_keys(const int64_t* __restrict__ ids, int F, int B, uint32_t* __re
   }
 }
 
-__global__ void __cluster_dims__(kCS, 1, 1) __launch_bounds__(kCT, 1)
+template <int kCS, int kCT>
+__global__ void __cluster_dims__(kCS, 1, 1) __launch_bounds__(kCT, 1024 / kCT)   // 64 registers per thread either way
 k_cluster_sort(const int64_t* __restrict__ ids, const uint32_t* __restrict__ keys_fm, int F, int B, int chunk,
                int passes, uint32_t* __restrict__ keys_out, int32_t* __restrict__ order,
                uint32_t* __restrict__ tile_heads, FusedUnique fu) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ unsigned s_misc[4];    // [0] field of this cluster (rank 0's copy), [1] heads of this CTA, [2] ids before this field
-  __shared__ unsigned s_wsum[kCW];
+  constexpr int kCW = kCT / 32;
+  __shared__ unsigned s_wsum[32];
   cg::cluster_group cluster = cg::this_cluster();
   const int r = (int)cluster.block_rank();
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -374,12 +376,7 @@ k_cluster_sort(const int64_t* __restrict__ ids, const uint32_t* __restrict__ key
 
   const unsigned lt = edl_lanemask_lt();
   const int n_local = min(max(B - p0, 0), chunk);      // valid positions of this CTA (a prefix)
-  unsigned krem[kCS], vrem[kCS];                       // kbuf0 / vbuf0 of every CTA of the cluster (shared::cluster window)
-#pragma unroll
-  for (int rr = 0; rr < kCS; ++rr) {
-    asm("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(krem[rr]) : "r"((unsigned)__cvta_generic_to_shared(kbuf0)), "r"(rr));
-    asm("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(vrem[rr]) : "r"((unsigned)__cvta_generic_to_shared(vbuf0)), "r"(rr));
-  }
+  const unsigned kloc = (unsigned)__cvta_generic_to_shared(kbuf0), vloc = (unsigned)__cvta_generic_to_shared(vbuf0);
   for (int pass = 0; pass < passes; ++pass) {
     // Every pass: kbuf0 / vbuf0 -> (ranked, grouped by digit) kbuf1 / vbuf1 of THIS CTA -> kbuf0 / vbuf0 of the
     // CTAs that own the destinations.  Grouping locally first makes the stores into the other CTAs' shared
@@ -509,12 +506,15 @@ k_cluster_sort(const int64_t* __restrict__ ids, const uint32_t* __restrict__ key
         const int q = (h + k) * kCT + tid;
         if (h + k < iters && q < n_local) {
           const unsigned p = cp[k];
-          const unsigned rr = (p >= (unsigned)chunk) + (p >= 2u * chunk) + (p >= 3u * chunk);
+          unsigned rr = 0;
+#pragma unroll
+          for (int i = 1; i < kCS; ++i) rr += p >= (unsigned)(i * chunk) ? 1u : 0u;
           const unsigned off = p - rr * chunk;
-          const unsigned ka = rr < 2 ? (rr == 0 ? krem[0] : krem[1]) : (rr == 2 ? krem[2] : krem[3]);
-          const unsigned va = rr < 2 ? (rr == 0 ? vrem[0] : vrem[1]) : (rr == 2 ? vrem[2] : vrem[3]);
-          asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(ka + off * 4u), "r"(ck[k]) : "memory");
-          asm volatile("st.shared::cluster.u16 [%0], %1;" ::"r"(va + off * 2u), "h"(cv[k]) : "memory");
+          unsigned ka, va;       // the same offsets in CTA rr's shared memory (shared::cluster window)
+          asm("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ka) : "r"(kloc + off * 4u), "r"(rr));
+          asm("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(va) : "r"(vloc + off * 2u), "r"(rr));
+          asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(ka), "r"(ck[k]) : "memory");
+          asm volatile("st.shared::cluster.u16 [%0], %1;" ::"r"(va), "h"(cv[k]) : "memory");
         }
       }
     }
@@ -546,7 +546,7 @@ k_cluster_sort(const int64_t* __restrict__ ids, const uint32_t* __restrict__ key
     if (lane == 0) s_wsum[w] = wtot;
     __syncthreads();
     if (w == 0) {
-      const unsigned v = s_wsum[lane];
+      const unsigned v = lane < kCW ? s_wsum[lane] : 0u;
       unsigned inc = v;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -794,7 +794,7 @@ FmPlan fm_plan(int64_t n, const int32_t* n_dev, const int64_t* field_base, int n
   FmPlan f{false, 1, n, n, 0, false};
   if (field_bits <= 0 || !field_base || n_fields <= 1 || n_dev || n % n_fields != 0) return f;
   // worth it when a radix pass is saved, or when the fields are small enough for k_cluster_sort
-  const bool in_cluster = field_bits <= 32 && n / n_fields <= (int64_t)kCS * kCCap && edl_tune(EDL_TUNE_DEDUP_IMPL) >= 1;
+  const bool in_cluster = field_bits <= 32 && n / n_fields <= (int64_t)kClusterMaxField && edl_tune(EDL_TUNE_DEDUP_IMPL) >= 1;
   if ((field_bits + 7) / 8 >= (key_bits + 7) / 8 && !in_cluster) return f;
   f.on = true;
   f.in_cluster = in_cluster;
@@ -840,7 +840,8 @@ void rowscan(uint32_t* hist, int n_tiles, uint32_t* tot, int tps, int n_seg, cud
     k_rowscan<<<256 * n_seg, kThreads, 0, st>>>(hist, n_tiles, tot, tps);
 }
 
-// k_cluster_sort needs more dynamic shared memory than the default limit: raised once per device.
+// k_cluster_sort needs more dynamic shared memory than the default limit: raised once per device and shape.
+template <int kCS, int kCT>
 int cluster_sort_prepare() {
   static std::mutex mu;
   static bool done[64] = {false};
@@ -849,10 +850,23 @@ int cluster_sort_prepare() {
   EDL_REQUIRE(dev >= 0 && dev < 64, EDL_ELIMIT, "edl_unique: device ordinal %d beyond 64", dev);
   std::lock_guard<std::mutex> lock(mu);
   if (!done[dev]) {
-    EDL_CUDA(cudaFuncSetAttribute(k_cluster_sort, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)cluster_sort_smem(kCCap)));
+    EDL_CUDA(cudaFuncSetAttribute(k_cluster_sort<kCS, kCT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)cluster_sort_smem(kClusterMaxField / kCS, kCT / 32)));
     done[dev] = true;
   }
+  return EDL_OK;
+}
+
+template <int kCS, int kCT>
+int cluster_sort_launch(const int64_t* ids, const uint32_t* keys_fm, int F, int64_t B, int passes, uint32_t* keys_out,
+                        int32_t* order, uint32_t* tile_heads, bool* heads_done, const FusedUnique& fu, cudaStream_t st) {
+  const int chunk = (int)(edl_cdiv(edl_cdiv(B, kCS), kCT) * kCT);
+  int rc = cluster_sort_prepare<kCS, kCT>();
+  if (rc) return rc;
+  *heads_done = !fu.on && B % kTile == 0 && chunk % kTile == 0;
+  k_cluster_sort<kCS, kCT><<<F * kCS, kCT, cluster_sort_smem(chunk, kCT / 32), st>>>(
+      ids, keys_fm, F, (int)B, chunk, passes, keys_out, order, *heads_done ? tile_heads : (uint32_t*)nullptr, fu);
+  EDL_LAUNCH_CHECK("k_cluster_sort");
   return EDL_OK;
 }
 
@@ -876,10 +890,6 @@ int unique_impl(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64
   bool in_cluster = false;
   if constexpr (std::is_same<KeyT, uint32_t>::value) {
     if (fm.on && fm.in_cluster) {
-      const int chunk = (int)(edl_cdiv(edl_cdiv(fm.B, kCS), kCW * 32) * (kCW * 32));
-      const size_t smem = cluster_sort_smem(chunk);
-      int rc = cluster_sort_prepare();
-      if (rc) return rc;
       const int mode = edl_tune(EDL_TUNE_DEDUP_IMPL);
       // ids -> field-major 32-bit keys first (in the second key buffer, which this path does not use otherwise)
       const uint32_t* keys_fm = nullptr;
@@ -895,10 +905,12 @@ int unique_impl(const int64_t* ids, int64_t n, const int32_t* n_dev, const int64
         fu = FusedUnique{1, uniq, seg_offsets, seg_first, inverse, n_unique, field_base, (unsigned*)W.tot,
                          (unsigned long long*)(W.tot + 2)};
       }
-      heads_done = !fu.on && fm.B % kTile == 0 && chunk % kTile == 0;
-      k_cluster_sort<<<fm.F * kCS, kCT, smem, st>>>(ids, keys_fm, fm.F, (int)fm.B, chunk, passes, (uint32_t*)kbuf[0],
-                                                    order, heads_done ? W.tile_heads : (uint32_t*)nullptr, fu);
-      EDL_LAUNCH_CHECK("k_cluster_sort");
+      const int rc = edl_tune(EDL_TUNE_DEDUP_SHAPE) == 1
+                         ? cluster_sort_launch<8, 512>(ids, keys_fm, fm.F, fm.B, passes, (uint32_t*)kbuf[0], order,
+                                                       W.tile_heads, &heads_done, fu, st)
+                         : cluster_sort_launch<4, 1024>(ids, keys_fm, fm.F, fm.B, passes, (uint32_t*)kbuf[0], order,
+                                                        W.tile_heads, &heads_done, fu, st);
+      if (rc) return rc;
       if (fu.on) {
         if (counts) {
           int g = (int)std::min<int64_t>(edl_cdiv(n, 256), EDL_SM_COUNT * 8);

@@ -160,7 +160,8 @@ def unique_launches(n: int, n_fields: int, key_bits: int, field_bits: int = 0, *
             transposed = 1 if n_fields * 129 * 4 <= 48 * 1024 else 0
             if impl == 2:
                 return transposed + 1 + extra
-            chunk = ((B + 3) // 4 + 1023) // 1024 * 1024
+            cs, ct = (8, 512) if _lib.tuning_get("dedup_shape") == 1 else (4, 1024)
+            chunk = ((B + cs - 1) // cs + ct - 1) // ct * ct
             heads_fused = B % 2048 == 0 and chunk % 2048 == 0
             return transposed + 1 + (0 if heads_fused else 1) + 2 + extra
         if passes_fm < passes_flat:

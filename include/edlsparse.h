@@ -78,6 +78,7 @@ const char* edl_last_error_string(void);
  *                                         field sorted by one thread-block cluster in shared memory, which also
  *                                         writes the unique step's outputs; 1 = the same sort, unique step as
  *                                         separate kernels; 0 = the global counting-sort passes
+ *   dedup_shape   (EDL_DEDUP_SHAPE, 0)    that cluster: 0 = 4 CTAs x 1024 threads per field, 1 = 8 CTAs x 512 threads
  * Unknown names and out-of-range values return EDL_EINVAL. */
 int edl_tuning_set(const char* name, int value);
 int edl_tuning_get(const char* name, int* value_out);

@@ -98,18 +98,19 @@ def test_unique_fused_fields_equals_per_table(cuda):
     assert np.array_equal(uniq, cat)
 
 
-@pytest.mark.parametrize("impl", [2, 1, 0])
+@pytest.mark.parametrize("impl,shape", [(2, 0), (2, 1), (1, 0), (1, 1), (0, 0)])
 @pytest.mark.parametrize("B,rows", [(1, [5, 9]), (37, [1000, 50, 7777, 3]), (2048, [300, 300, 70000]),
                                     (2049, [1 << 20, 11]), (5000, [10_000_000] * 26), (4096, [40_000_000] * 5),
                                     (8192, [60000] * 7), (65536, [100, 100]), (65536, [10_000_000] * 26),
                                     (32768, [40_000_000] * 26), (65537, [1 << 20] * 3), (65535, [1 << 24, 3]),
-                                    (3072, [1 << 31, 1 << 31])])
-def test_unique_field_major_mode(cuda, B, rows, impl):
+                                    (3072, [1 << 31, 1 << 31]), (65536, [1 << 20] * 40)])   # 40 clusters: two waves
+def test_unique_field_major_mode(cuda, B, rows, impl, shape):
     """field_bits > 0: per-field sort on the per-field id bits -- identical outputs to the flat sort.
     impl 1 / 2: fields of at most 65536 samples are sorted by k_cluster_sort (one cluster per field, 1..4 passes
     in shared memory); 2 lets that kernel write the unique step's outputs as well (fields handed out by ticket,
     per-field totals passed on through global memory), 1 runs the unique kernels after it (head count fused
-    when the tiles line up); impl 0 and larger fields: the global passes."""
+    when the tiles line up); impl 0 and larger fields: the global passes.  shape: 4 CTAs x 1024 threads or
+    8 CTAs x 512 threads per field."""
     from easydl_b200 import _lib
     from easydl_b200 import kernels as K
     from easydl_b200.criteo import CriteoSynthetic
@@ -118,13 +119,15 @@ def test_unique_field_major_mode(cuda, B, rows, impl):
     keys = O.fuse_keys(ids, bases)
     key_bits = int(bases[-1] - 1).bit_length()
     field_bits = max(1, int(max(rows) - 1).bit_length())
-    saved = _lib.tuning_get("dedup_impl")
+    saved = _lib.tuning_get("dedup_impl"), _lib.tuning_get("dedup_shape")
     _lib.tuning_set("dedup_impl", impl)
+    _lib.tuning_set("dedup_shape", shape)
     try:
         r = K.unique(dev(ids, cuda).view(-1), dev(bases[:len(rows)], cuda), key_bits, field_bits=field_bits)
         U = r.count()
     finally:
-        _lib.tuning_set("dedup_impl", saved)
+        _lib.tuning_set("dedup_impl", saved[0])
+        _lib.tuning_set("dedup_shape", saved[1])
     uniq, inv, cnt, order, seg = O.dedup(keys)
     assert U == len(uniq)
     assert np.array_equal(r.uniq[:U].cpu().numpy(), uniq)

@@ -27,7 +27,7 @@ DEFAULT_SETS = (
     "seg_impl=1,stream_ctas=3,long_thr=16,classify_side=0;"
     "seg_impl=1,stream_ctas=3,long_thr=16,seg_fork=0"
 )
-KNOBS = ("long_thr", "seg_fork", "classify_side", "seg_impl", "stream_ctas", "stream_stages", "direct_batch", "gather_impl", "dedup_impl")
+KNOBS = ("long_thr", "seg_fork", "classify_side", "seg_impl", "stream_ctas", "stream_stages", "direct_batch", "gather_impl", "dedup_impl", "dedup_shape")
 
 
 def apply(setting, defaults):
