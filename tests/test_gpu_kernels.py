@@ -103,7 +103,8 @@ def test_unique_fused_fields_equals_per_table(cuda):
                                     (2049, [1 << 20, 11]), (5000, [10_000_000] * 26), (4096, [40_000_000] * 5),
                                     (8192, [60000] * 7), (65536, [100, 100]), (65536, [10_000_000] * 26),
                                     (32768, [40_000_000] * 26), (65537, [1 << 20] * 3), (65535, [1 << 24, 3]),
-                                    (3072, [1 << 31, 1 << 31]), (65536, [1 << 20] * 40)])   # 40 clusters: two waves
+                                    (3072, [1 << 31, 1 << 31]), (65536, [1 << 20] * 40),   # 40 clusters: two waves
+                                    (300, [5000] * 100)])      # too many fields for the transposing tile: ids read in place
 def test_unique_field_major_mode(cuda, B, rows, impl, shape):
     """field_bits > 0: per-field sort on the per-field id bits -- identical outputs to the flat sort.
     impl 1 / 2: fields of at most 65536 samples are sorted by k_cluster_sort (one cluster per field, 1..4 passes
