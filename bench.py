@@ -624,7 +624,8 @@ def run_b200_arm(a):
             t_lk = phases["lookup_ms"] * 1e-3
             ach = update_b / t_up / 1e9
             line["roofline"] = {
-                "kernel": ("k_seg_direct" if a.dim < 128 else "k_seg_stream") +
+                "kernel": ("k_seg_stream" if (a.dim >= 256 and N >= (256 << 10)) or (a.dim >= 128 and N >= (1 << 20))
+                           else "k_seg_direct") +   # seg_direct.cuh, launch_direct: the library's own choice
                           " || (k_seg_classify -> k_seg_chunk -> k_seg_long_final) (segmented reduce + "
                           "row update: four launches per step, hot-id kernels on a forked branch, timed together)",
                 "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,

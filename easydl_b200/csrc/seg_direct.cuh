@@ -364,11 +364,18 @@ int launch_direct(const void* grad, const void* grad32, int D4, const int32_t* o
   const int long_thr = std::max(kLongThrMin, edl_tune(EDL_TUNE_LONG_THR));
   const int batch = edl_tune(EDL_TUNE_DIRECT_BATCH);
   const int fork = edl_tune(EDL_TUNE_SEG_FORK);
-  // seg_impl 2 (default): the register path for fp32 gradient rows of fewer than 128 floats; the streamed
-  // kernel for float64 / mixed rows (the owner side of the sharded step) and for rows of 512 bytes and more,
-  // where the register path holds too few bytes in flight per warp (dim 256: 997 -> 787 us, r2_experiments 7)
+  // seg_impl 2 (default) picks by row type, row width and size of the call (profiles/r2_experiments.md 7):
+  // the streamed kernel for float64 / mixed rows (the owner side of the sharded step) and for wide fp32 rows
+  // when there are enough ids to keep its persistent warps fed -- rows of 1 KB from 256 K ids up (dim 256, batch
+  // 256K: 0.99 of the measured copy peak against 0.71), rows of 512 B from 1 M ids up -- the register path
+  // otherwise (it holds too few bytes in flight per warp for wide rows, but wins on 256-byte rows and small calls).
   int impl = edl_tune(EDL_TUNE_SEG_IMPL);
-  if (impl == 2) impl = (std::is_same<GT, float>::value && D4 < 32) ? 0 : 1;
+  if (impl == 2) {
+    if (!std::is_same<GT, float>::value) impl = 1;
+    else if (D4 >= 64) impl = max_unique >= (256 << 10) ? 1 : 0;
+    else if (D4 >= 32) impl = max_unique >= (1 << 20) ? 1 : 0;
+    else impl = 0;
+  }
   const bool cls_side = fork && edl_tune(EDL_TUNE_CLASSIFY_SIDE);
   const bool classify = fork || impl == 1;   // k_seg_direct can list the hot ids itself (unforked launch)
   std::unique_lock<std::mutex> lock(fork_mutex(), std::defer_lock);

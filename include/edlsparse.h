@@ -67,9 +67,9 @@ const char* edl_last_error_string(void);
  *   seg_fork      (EDL_SEG_FORK, 1)       hot-id kernels on the helper stream beside the main reduce kernel
  *   classify_side (EDL_CLASSIFY_SIDE, 1)  forked launch: the hot-id listing runs on the helper stream too
  *   seg_impl      (EDL_SEG_IMPL, 2)       main reduce kernel: 0 = k_seg_direct (register path), 1 = k_seg_stream
- *                                         (cp.async ring), 2 = k_seg_direct for fp32 gradient rows narrower than 128
- *                                         floats, k_seg_stream for wider rows and for float64 / mixed rows
- *                                         (measured best for each)
+ *                                         (cp.async ring), 2 = k_seg_stream for float64 / mixed gradient rows and
+ *                                         for fp32 rows of 128 floats and more in large calls (>= 1 M ids; >= 256 K
+ *                                         ids at 256 floats), k_seg_direct otherwise (measured best for each)
  *   stream_ctas   (EDL_STREAM_CTAS, 3)    k_seg_stream: persistent CTAs per SM (capped by shared memory)
  *   stream_stages (EDL_STREAM_STAGES, 4)  k_seg_stream: ring slots in use, 2..4 (bytes in flight per warp)
  *   direct_batch  (EDL_DIRECT_BATCH, 2)   k_seg_direct: ids per lane group
