@@ -78,6 +78,8 @@ PROTOTYPES = {
     "edl_slot_positions": (_int, [_p, _i64, _p, _p, _int, _i64, _p, _p]),
     "edl_slot_compact": (_int, [_p, _p, _int, _i64, _i64, _p, _p, _p, _p]),
     "edl_remap_index": (_int, [_p, _p, _i64, _p, _p, _p]),
+    "edl_slot_merge_unique_workspace_bytes": (_sz, [_int, _i64]),
+    "edl_slot_merge_unique": (_int, [_p, _p, _int, _i64, _i64, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "edl_expand_window": (_int, [_p, _int, _p, _i64, _int, _int, _int, _p, _p]),
 }
 

@@ -1007,6 +1007,108 @@ extern "C" int edl_unique(const int64_t* ids, int64_t n, const int32_t* n_dev,
                                order, seg_offsets, seg_first, n_unique, W, st);
 }
 
+// ------------------------------------------------------- A1 on the owner side of the slot exchange
+// The owner's keys arrive as S slots, slot s holding what rank s sent: strictly increasing keys (a stable
+// partition of a sorted unique list).  The stable sorted order of their concatenation therefore needs no sort:
+// an element's place is its place in its own run plus, for every other run, the number of keys there that go
+// before it (smaller key; equal key in a lower slot) -- S - 1 binary searches over L2-resident runs.  One
+// kernel replaces edl_slot_compact + the four radix passes of edl_unique + the two edl_remap_index calls: it
+// writes the sorted keys and, as `order`, the slot-space rows (bit 30: the gradient row is an fp32 row), so
+// the unique kernels behind it emit seg_first in slot space as well.
+namespace {
+constexpr int kMergeMaxSlots = 64;
+
+__global__ void __launch_bounds__(kThreads)
+k_slot_merge(const long long* __restrict__ slots, const int32_t* __restrict__ counts, int S, long long stride,
+             long long limit, uint64_t* __restrict__ sorted, uint32_t* __restrict__ order, int32_t* __restrict__ n_out) {
+  __shared__ int start[kMergeMaxSlots + 1];
+  if (threadIdx.x == 0) {
+    int acc = 0;
+    for (int s = 0; s < S; ++s) {
+      start[s] = acc;
+      const int c = counts[s];
+      acc += (int)(c > limit ? limit : (c < 0 ? 0 : c));
+    }
+    start[S] = acc;
+    if (blockIdx.x == 0) *n_out = acc;
+  }
+  __syncthreads();
+  const int total = start[S];
+  for (int i = (int)blockIdx.x * kThreads + threadIdx.x; i < total; i += (int)gridDim.x * kThreads) {
+    int s = 0;
+    while (start[s + 1] <= i) ++s;          // S <= 64, shared memory
+    const int j = i - start[s];
+    const long long src = (long long)s * stride + j;
+    const long long raw = slots[src];
+    const long long k = raw & ~EDL_KEY_FLAG_SINGLE;
+    int pos = j;
+    for (int t = 0; t < S; ++t) {
+      if (t == s) continue;
+      const long long* run = slots + (long long)t * stride;
+      int lo = 0, hi = start[t + 1] - start[t];
+      while (lo < hi) {                     // elements of run t in front of (k, slot s)
+        const int mid = (lo + hi) >> 1;
+        const long long v = run[mid] & ~EDL_KEY_FLAG_SINGLE;
+        if (v < k || (v == k && t < s)) lo = mid + 1; else hi = mid;
+      }
+      pos += lo;
+    }
+    sorted[pos] = (uint64_t)k;
+    order[pos] = (uint32_t)src | (((raw >> 62) & 1) ? (1u << 30) : 0u);
+  }
+}
+
+struct MergeWs { uint64_t* sorted; uint32_t* tile_heads; size_t bytes; };
+MergeWs carve_merge(void* ws, int64_t cap) {
+  const int64_t tiles = edl_cdiv(cap > 0 ? cap : 1, kTile);
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = edl_align_up(off + bytes, 256); return o; };
+  const size_t oS = take((size_t)cap * 8), oT = take((size_t)(tiles + 1) * 4);
+  MergeWs r;
+  r.sorted = (uint64_t*)((char*)ws + oS); r.tile_heads = (uint32_t*)((char*)ws + oT); r.bytes = off;
+  return r;
+}
+}  // namespace
+
+extern "C" size_t edl_slot_merge_unique_workspace_bytes(int num_slots, int64_t slot_limit) {
+  if (num_slots < 1 || slot_limit < 0) return 0;
+  return carve_merge(nullptr, (int64_t)num_slots * slot_limit).bytes;
+}
+
+extern "C" int edl_slot_merge_unique(const int64_t* keys_slots, const int32_t* counts_dev, int num_slots,
+                                     int64_t slot_stride, int64_t slot_limit, int64_t* uniq, int32_t* order,
+                                     int32_t* seg_offsets, int32_t* seg_first, int32_t* n_unique, int32_t* n_out_dev,
+                                     void* workspace, size_t workspace_bytes, edl_stream_t stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  EDL_REQUIRE(keys_slots && counts_dev && uniq && order && seg_offsets && n_unique && n_out_dev, EDL_EINVAL,
+              "edl_slot_merge_unique: null pointer");
+  EDL_REQUIRE(num_slots >= 1 && num_slots <= kMergeMaxSlots, EDL_EINVAL, "edl_slot_merge_unique: num_slots=%d out of [1, %d]",
+              num_slots, kMergeMaxSlots);
+  EDL_REQUIRE(slot_stride > 0 && slot_limit >= 0 && slot_limit <= slot_stride, EDL_EINVAL, "edl_slot_merge_unique: bad slot sizes");
+  const int64_t cap = slot_limit * num_slots;
+  EDL_REQUIRE(slot_stride * num_slots < (int64_t)(1 << 30) && cap < (int64_t)(1 << 30), EDL_ELIMIT,
+              "edl_slot_merge_unique: slots do not fit a 30-bit row index");
+  if (cap == 0) {
+    k_empty_unique<<<1, 1, 0, st>>>(n_unique, seg_offsets);
+    EDL_CUDA(cudaMemsetAsync(n_out_dev, 0, 4, st));
+    EDL_LAUNCH_CHECK("k_empty_unique");
+    return EDL_OK;
+  }
+  MergeWs W = carve_merge(workspace, cap);
+  EDL_REQUIRE(workspace && workspace_bytes >= W.bytes, EDL_EWORKSPACE, "edl_slot_merge_unique: workspace %zu < required %zu",
+              workspace_bytes, W.bytes);
+  const int g = (int)std::min<int64_t>(edl_cdiv(cap, kThreads), EDL_SM_COUNT * 8);
+  k_slot_merge<<<g, kThreads, 0, st>>>((const long long*)keys_slots, counts_dev, num_slots, (long long)slot_stride,
+                                       (long long)slot_limit, W.sorted, (uint32_t*)order, n_out_dev);
+  const int tiles = (int)edl_cdiv(cap, kTile);
+  k_head_count<uint64_t><<<tiles, kThreads, 0, st>>>(W.sorted, cap, n_out_dev, W.tile_heads, 0);
+  k_scan_tiles<<<1, 1024, 0, st>>>(W.tile_heads, tiles, cap, n_out_dev, n_unique, seg_offsets);
+  k_unique_write<uint64_t><<<tiles, kThreads, 0, st>>>(W.sorted, (const uint32_t*)order, cap, n_out_dev, W.tile_heads, uniq,
+                                                       seg_offsets, seg_first, (int32_t*)nullptr, 0, (const int64_t*)nullptr);
+  EDL_LAUNCH_CHECK("slot merge + unique kernels");
+  return EDL_OK;
+}
+
 // --------------------------------------------------------------------------------- A2
 namespace {
 struct PartWs { uint8_t* dig; uint32_t* hist; uint32_t* tot; size_t bytes; };

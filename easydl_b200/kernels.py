@@ -313,6 +313,30 @@ def slot_compact(keys_slots: torch.Tensor, counts: torch.Tensor, slot_stride: in
                                _ptr(map_out), _ptr(n_out), _stream()), "edl_slot_compact")
 
 
+def slot_merge_unique(keys_slots: torch.Tensor, counts: torch.Tensor, slot_stride: int, slot_limit: int,
+                      out: UniqueResult, n_out: torch.Tensor, workspace: Optional[torch.Tensor] = None) -> UniqueResult:
+    """Owner side of the slot exchange in one call: the S sorted key slots merged into the dedup result
+    `out` (uniq, seg_offsets, n_unique; order and seg_first as slot-space rows with bit 30 = fp32 gradient
+    row) -- slot_compact + unique + 2 x remap_index without the sort."""
+    lib = _lib.load()
+    _need(keys_slots, torch.int64, "keys_slots")
+    _need(counts, torch.int32, "counts")
+    _need(n_out, torch.int32, "n_out")
+    S = counts.numel()
+    cap = S * slot_limit
+    if out.uniq.numel() < cap or out.order.numel() < cap or out.seg_offsets.numel() < cap + 1:
+        raise ValueError("slot_merge_unique: outputs smaller than num_slots * slot_limit")
+    if out.seg_first is not None and out.seg_first.numel() < cap:
+        raise ValueError("slot_merge_unique: seg_first smaller than num_slots * slot_limit")
+    need = lib.edl_slot_merge_unique_workspace_bytes(S, slot_limit)
+    if workspace is None or workspace.numel() < need:
+        workspace = _ws(need, keys_slots.device)
+    check(lib.edl_slot_merge_unique(_ptr(keys_slots), _ptr(counts), S, slot_stride, slot_limit, _ptr(out.uniq),
+                                    _ptr(out.order), _ptr(out.seg_offsets), _ptr(out.seg_first), _ptr(out.n_unique),
+                                    _ptr(n_out), _ptr(workspace), workspace.numel(), _stream()), "edl_slot_merge_unique")
+    return out
+
+
 def remap_index(index: torch.Tensor, mapping: torch.Tensor, n_dev: Optional[torch.Tensor],
                 out: Optional[torch.Tensor] = None):
     lib = _lib.load()

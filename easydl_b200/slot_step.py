@@ -215,7 +215,14 @@ class SlotShardedStep:
             self.first_w = torch.empty(N, **i32)
         self.ws_u1 = torch.empty(lib.edl_unique_workspace_bytes(N, self.key_bits, self.F, self.field_bits),
                                  dtype=torch.uint8, device=dev)
-        self.ws_u2 = torch.empty(lib.edl_unique_workspace_bytes(R, self.key_bits, 0, 0), dtype=torch.uint8, device=dev)
+        self.ws_u2 = torch.empty(max(lib.edl_unique_workspace_bytes(R, self.key_bits, 0, 0),
+                                     lib.edl_slot_merge_unique_workspace_bytes(self.S, self.limit)),
+                                 dtype=torch.uint8, device=dev)
+        # owner-side dedup: merge of the S sorted slots (default) or compact + radix sort + remaps (EDL_SLOT_OWNER_MERGE=0)
+        self.owner_merge = os.environ.get("EDL_SLOT_OWNER_MERGE", "1") == "1"
+        self.uq2_slot = K.UniqueResult(uniq=self.uq2.uniq, inverse=None, counts=None, order=self.order2,
+                                       seg_offsets=self.uq2.seg_offsets, n_unique=self.uq2.n_unique, n=R,
+                                       seg_first=self.first2)
         self.ws_part = torch.empty(lib.edl_partition_mod_workspace_bytes(N, self.S), dtype=torch.uint8, device=dev)
         n_grad = self.B * self.F_total
         self.ws_seg = torch.empty(max(lib.edl_segreduce_workspace_bytes(N, n_grad, self.dim),
@@ -238,7 +245,8 @@ class SlotShardedStep:
         # A: unique, partition 4, send 1; B: S gathers; C: positions, compose, expand, 2 torch ops, reduce 4;
         # D: compact, unique, 2 remaps, update 4; 3 fences
         self.launches_per_step = (K.unique_launches(N, self.F, self.key_bits, self.field_bits) + 4 + 1 + self.S + 3 + 2 + 4
-                                  + 1 + K.unique_launches(N, 0, self.key_bits, n_dev=True) + 2 + 4 + 3)
+                                  + (4 if self.owner_merge else 1 + K.unique_launches(N, 0, self.key_bits, n_dev=True) + 2)
+                                  + 4 + 3)
 
     # ------------------------------------------------------------------ phases
     def phase_a(self, ids: torch.Tensor, front=None, gen: Optional[int] = None):
@@ -314,6 +322,10 @@ class SlotShardedStep:
     def phase_d_prepare(self):
         """Needs only the received keys (fence 1): compact, dedup, slot-space order."""
         b, g, uq2 = self.buf, self.gen, self.uq2
+        if self.owner_merge:      # every slot holds a sorted run: merge them (4 launches instead of 18)
+            K.slot_merge_unique(b.own_region(g, "keys"), b.own_region(g, "counts"), b.stride, self.limit,
+                                self.uq2_slot, self.n_recv, workspace=self.ws_u2)
+            return
         K.slot_compact(b.own_region(g, "keys"), b.own_region(g, "counts"), b.stride, self.limit, self.keys_c,
                        self.map_c, self.n_recv)
         K.unique(self.keys_c, None, self.key_bits, want_inverse=False, want_counts=False, n_dev=self.n_recv,

@@ -354,13 +354,25 @@ int edl_peer_signal_wait_counter(const int64_t* peer_flag_ptrs_dev, int64_t* own
  *                    slot (= peer rank) order with bit 62 cleared, map_out[i] = slot-space row of
  *                    keys_out[i], with bit 30 set where the key carried bit 62, and *n_out.
  * edl_remap_index  : out[i] = map[index[i]] for i < *n_dev (edl_compose_index with a device count):
- *                    turns the `order` / `seg_first` of edl_unique(keys_out) into slot-space rows. */
+ *                    turns the `order` / `seg_first` of edl_unique(keys_out) into slot-space rows.
+ * edl_slot_merge_unique: the three calls above in one (edl_slot_compact -> edl_unique -> edl_remap_index x 2) for
+ *                    slots whose keys are strictly increasing (what edl_partition_mod + edl_slot_send deliver from
+ *                    an edl_unique result): the runs are MERGED (S - 1 binary searches per key) instead of sorted.
+ *                    uniq / seg_offsets / n_unique as edl_unique of the concatenated keys would give them; order and
+ *                    seg_first already as slot-space rows (bit 30 = the key carried bit 62); *n_out_dev = keys
+ *                    received.  Arrays of num_slots * slot_limit entries (seg_offsets one more).  Keys out of
+ *                    order inside a slot give an unspecified result: the caller guarantees the precondition. */
 int edl_slot_send(const void* rows, int row_bytes, const int32_t* offsets_dev, int num_slots,
                   const int64_t* dst_bases_dev, int64_t slot_limit, const int64_t* count_ptrs_dev,
                   int32_t* err_dev, int64_t n_max, const int32_t* flag_seg_offsets, const int32_t* flag_perm,
                   edl_stream_t stream);
 int edl_slot_positions(const int32_t* pos, int64_t n_max, const int32_t* n_dev, const int32_t* offsets_dev,
                        int num_slots, int64_t slot_stride, int32_t* out, edl_stream_t stream);
+size_t edl_slot_merge_unique_workspace_bytes(int num_slots, int64_t slot_limit);
+int edl_slot_merge_unique(const int64_t* keys_slots, const int32_t* counts_dev, int num_slots, int64_t slot_stride,
+                          int64_t slot_limit, int64_t* uniq, int32_t* order, int32_t* seg_offsets, int32_t* seg_first,
+                          int32_t* n_unique, int32_t* n_out_dev, void* workspace, size_t workspace_bytes,
+                          edl_stream_t stream);
 int edl_slot_compact(const int64_t* keys_slots, const int32_t* counts_dev, int num_slots, int64_t slot_stride,
                      int64_t slot_limit, int64_t* keys_out, int32_t* map_out, int32_t* n_out_dev,
                      edl_stream_t stream);

@@ -66,6 +66,65 @@ def test_slot_send_positions_compact_remap(cuda):
     assert int(err.item()) == 1 and counts.cpu().tolist() == [17, 0, 20]
 
 
+@pytest.mark.parametrize("S,limit,hi", [(1, 100, 50), (2, 5000, 20000), (3, 64, 40), (8, 3000, 9000), (8, 20000, 1 << 27),
+                                        (64, 300, 5000)])
+def test_slot_merge_unique_equals_compact_sort_remap(cuda, S, limit, hi):
+    """edl_slot_merge_unique (the owner's S sorted key slots merged) against the calls it replaces --
+    edl_slot_compact -> edl_unique -> edl_remap_index x 2 -- and against the oracle's dedup of the
+    concatenated keys: empty slots, a count beyond the limit (cut there), keys marked with bit 62."""
+    from easydl_b200 import kernels as K
+    rng = np.random.default_rng(S * 1000 + limit)
+    stride = limit + 7
+    slots = np.zeros(S * stride, dtype=np.int64)
+    counts = np.zeros(S, dtype=np.int32)
+    runs = []
+    for s in range(S):
+        n = 0 if (s == 1 and S > 2) else int(rng.integers(1, min(limit, hi) + 1))
+        run = np.unique(rng.integers(0, hi, size=n, dtype=np.int64))
+        n = len(run)
+        flags = rng.integers(0, 2, size=n).astype(np.int64) << 62
+        slots[s * stride:s * stride + n] = run | flags
+        counts[s] = n
+        runs.append(run)
+    if S > 1:                       # a sender that reports more than the slot holds: cut at the limit
+        full = np.unique(rng.integers(0, max(hi, 4 * limit), size=8 * limit, dtype=np.int64))[:limit]
+        assert len(full) == limit
+        slots[(S - 1) * stride:(S - 1) * stride + limit] = full
+        counts[S - 1] = limit + 5
+        runs[S - 1] = full
+    R = S * limit
+    d_slots, d_counts = dev(slots, cuda), dev(counts, cuda)
+    i32 = dict(dtype=torch.int32, device=cuda)
+
+    def result():
+        return K.UniqueResult(uniq=torch.empty(R, dtype=torch.int64, device=cuda), inverse=None, counts=None,
+                              order=torch.empty(R, **i32), seg_offsets=torch.empty(R + 1, **i32),
+                              n_unique=torch.zeros(1, **i32), n=R, seg_first=torch.empty(R, **i32))
+    # the calls it replaces
+    keys_c, map_c, n_recv = torch.empty(R, dtype=torch.int64, device=cuda), torch.empty(R, **i32), torch.zeros(1, **i32)
+    K.slot_compact(d_slots, d_counts, stride, limit, keys_c, map_c, n_recv)
+    ref = K.unique(keys_c, None, 63, want_inverse=False, want_counts=False, n_dev=n_recv, out=result())
+    order_ref = K.remap_index(ref.order, map_c, n_recv, out=torch.empty(R, **i32))
+    first_ref = K.remap_index(ref.seg_first, map_c, ref.n_unique, out=torch.empty(R, **i32))
+    # merged
+    got, n_out = result(), torch.zeros(1, **i32)
+    K.slot_merge_unique(d_slots, d_counts, stride, limit, got, n_out)
+    n, U = int(n_recv.item()), ref.count()
+    assert int(n_out.item()) == n == sum(len(r) for r in runs)
+    assert got.count() == U
+    assert torch.equal(got.uniq[:U], ref.uniq[:U])
+    assert torch.equal(got.seg_offsets[:U + 1], ref.seg_offsets[:U + 1])
+    assert torch.equal(got.order[:n], order_ref[:n])
+    assert torch.equal(got.seg_first[:U], first_ref[:U])
+    # and the oracle on the concatenation
+    uniq, _, _, order, seg = O.dedup(np.concatenate(runs) if n else np.zeros(0, dtype=np.int64))
+    assert np.array_equal(got.uniq[:U].cpu().numpy(), uniq)
+    assert np.array_equal(got.seg_offsets[:U + 1].cpu().numpy(), seg)
+    starts = np.concatenate([[0], np.cumsum([len(r) for r in runs])])
+    src = np.concatenate([s * stride + np.arange(len(r)) for s, r in enumerate(runs)]) if n else np.zeros(0, dtype=np.int64)
+    assert np.array_equal(got.order[:n].cpu().numpy() & ((1 << 30) - 1), src[order])
+
+
 def test_fence_with_device_counter_world_of_one(cuda):
     import ctypes as C
     from easydl_b200 import _lib
