@@ -605,7 +605,9 @@ def run_b200_arm(a):
             "config": config_for(a, world, U_mean, nb),
             "implementation": {
                 "code_path": ("sharded, lazily materialised rows" if a.lazy_rows else "sharded") if sharded else "single-shard fused",
-                "gradient_wire": a.wire if sharded else None, "exchange": (a.exchange if world > 1 else None)},
+                "gradient_wire": a.wire if sharded else None, "exchange": (a.exchange if world > 1 else None),
+                "owner_dedup": (("merge of the S sorted key slots" if os.environ.get("EDL_SLOT_OWNER_MERGE", "1") == "1"
+                                 else "radix sort of the received keys") if sharded and a.exchange.startswith("slots") else None)},
             "gpu_launches": step.launches_per_step * a.steps,
             "launch_mode": "cuda_graph" if graphed is not None else "eager",
             "step_pipelining": (("phase A (dedup, partition, key send) of batch i+1 beside the rounds of batch i" if sharded
