@@ -272,12 +272,12 @@ k_scatter(Loader ld, DigitFn dg, int64_t n, const int32_t* n_dev, int n_tiles,
 // ------------------------------------------------------------------ field sort inside one cluster
 // Field-major batches whose fields hold at most 65536 samples: the whole LSD sort of ONE field runs
 // inside ONE thread-block cluster, the field's (key, sample) pairs never leaving shared memory between
-// the passes.  CTA r of the cluster holds positions [r * chunk, (r + 1) * chunk) of the field in two
-// ping-pong buffers; a pass ranks its elements like k_scatter does (warp-striped, stable), publishes its
-// 256-bin histogram, reads the other CTAs' histograms through distributed shared memory, and stores every
-// element straight into the shared memory of the CTA that owns its destination.  One launch replaces the
-// 3 x (histogram, row scan, scatter) launches of the global path, and (when the tiles line up) the head
-// count of the unique step as well.
+// the passes.  CTA r of the cluster holds positions [r * chunk, (r + 1) * chunk) of the field; a pass ranks
+// its elements like k_scatter does (warp-striped, stable), groups them by digit in a second local buffer,
+// publishes its 256-bin histogram, reads the other CTAs' histograms through distributed shared memory, and
+// copies every digit group into the shared memory of the CTA(s) that own its destination.  One launch replaces
+// the 3 x (histogram, row scan, scatter) launches of the global path and, in its fused form, the three kernels
+// of the unique step as well (otherwise the head count, when the tiles line up).
 // Two shapes (template parameters kCS = CTAs per cluster, kCT = threads per CTA; knob dedup_shape):
 //   4 x 1024: 16384 positions and 215 KB of shared memory per CTA, one CTA per SM, the whole register file
 //   8 x 512 :  8192 positions and 107 KB per CTA, half the register file: other kernels' CTAs fit beside it
