@@ -1018,6 +1018,39 @@ extern "C" int edl_unique(const int64_t* ids, int64_t n, const int32_t* n_dev,
 namespace {
 constexpr int kMergeMaxSlots = 64;
 
+constexpr int kMK = 4;   // consecutive keys of a run per thread
+
+// does element v of a run go in front of key k of slot s?  smaller keys do, equal keys when the run's slot is lower
+__device__ __forceinline__ bool merge_before(long long v, long long k, bool lower_slot) {
+  v &= ~EDL_KEY_FLAG_SINGLE;
+  return v < k || (v == k && lower_slot);
+}
+// number of elements of run[lo0 .. len) in front of k, plus lo0: binary search
+__device__ __forceinline__ int merge_count(const long long* __restrict__ run, int lo0, int len, long long k, bool lower_slot) {
+  int lo = lo0, hi = len;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (merge_before(run[mid], k, lower_slot)) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+// the same when the answer is expected just behind `from` (the count of the thread's previous, smaller key):
+// doubling steps, then a binary search inside the last step
+__device__ __forceinline__ int merge_advance(const long long* __restrict__ run, int from, int len, long long k, bool lower_slot) {
+  if (from >= len || !merge_before(run[from], k, lower_slot)) return from;
+  int prev = from, step = 1;           // run[prev] goes in front of k
+  while (true) {
+    const int nx = prev + step;
+    if (nx >= len) return merge_count(run, prev + 1, len, k, lower_slot);
+    if (!merge_before(run[nx], k, lower_slot)) return merge_count(run, prev + 1, nx, k, lower_slot);
+    prev = nx;
+    step <<= 1;
+  }
+}
+
+// A thread places kMK consecutive keys: for every other run one binary search for its first key, then short walks
+// from there for the next ones (keys of a run ascend, so the counts do too) -- a third of the probes of a search
+// per key, and the probes, 32 different sectors per warp-wide load, are what this kernel's time is made of.
 __global__ void __launch_bounds__(kThreads)
 k_slot_merge(const long long* __restrict__ slots, const int32_t* __restrict__ counts, int S, long long stride,
              long long limit, uint64_t* __restrict__ sorted, uint32_t* __restrict__ order, int32_t* __restrict__ n_out) {
@@ -1034,27 +1067,43 @@ k_slot_merge(const long long* __restrict__ slots, const int32_t* __restrict__ co
   }
   __syncthreads();
   const int total = start[S];
-  for (int i = (int)blockIdx.x * kThreads + threadIdx.x; i < total; i += (int)gridDim.x * kThreads) {
+  for (int i0 = ((int)blockIdx.x * kThreads + threadIdx.x) * kMK; i0 < total; i0 += (int)gridDim.x * kThreads * kMK) {
+    long long key[kMK], raw[kMK], src[kMK];
+    int slot[kMK], pos[kMK];
     int s = 0;
-    while (start[s + 1] <= i) ++s;          // S <= 64, shared memory
-    const int j = i - start[s];
-    const long long src = (long long)s * stride + j;
-    const long long raw = slots[src];
-    const long long k = raw & ~EDL_KEY_FLAG_SINGLE;
-    int pos = j;
-    for (int t = 0; t < S; ++t) {
-      if (t == s) continue;
-      const long long* run = slots + (long long)t * stride;
-      int lo = 0, hi = start[t + 1] - start[t];
-      while (lo < hi) {                     // elements of run t in front of (k, slot s)
-        const int mid = (lo + hi) >> 1;
-        const long long v = run[mid] & ~EDL_KEY_FLAG_SINGLE;
-        if (v < k || (v == k && t < s)) lo = mid + 1; else hi = mid;
+#pragma unroll
+    for (int q = 0; q < kMK; ++q) {
+      const int i = i0 + q;
+      slot[q] = -1;
+      if (i < total) {
+        while (start[s + 1] <= i) ++s;    // S <= 64, shared memory
+        slot[q] = s;
+        pos[q] = i - start[s];
+        src[q] = (long long)s * stride + pos[q];
+        raw[q] = slots[src[q]];
+        key[q] = raw[q] & ~EDL_KEY_FLAG_SINGLE;
       }
-      pos += lo;
     }
-    sorted[pos] = (uint64_t)k;
-    order[pos] = (uint32_t)src | (((raw >> 62) & 1) ? (1u << 30) : 0u);
+    for (int t = 0; t < S; ++t) {
+      const long long* run = slots + (long long)t * stride;
+      const int len = start[t + 1] - start[t];
+      int c = -1;                         // count for the previous key of the same slot, if any
+#pragma unroll
+      for (int q = 0; q < kMK; ++q) {
+        if (slot[q] < 0) continue;
+        if (slot[q] == t) { c = -1; continue; }
+        const bool lower = t < slot[q];
+        if (c < 0 || slot[q] != slot[q - (q > 0)]) c = merge_count(run, 0, len, key[q], lower);
+        else c = merge_advance(run, c, len, key[q], lower);
+        pos[q] += c;
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < kMK; ++q) {
+      if (slot[q] < 0) continue;
+      sorted[pos[q]] = (uint64_t)key[q];
+      order[pos[q]] = (uint32_t)src[q] | (((raw[q] >> 62) & 1) ? (1u << 30) : 0u);
+    }
   }
 }
 
@@ -1097,7 +1146,7 @@ extern "C" int edl_slot_merge_unique(const int64_t* keys_slots, const int32_t* c
   MergeWs W = carve_merge(workspace, cap);
   EDL_REQUIRE(workspace && workspace_bytes >= W.bytes, EDL_EWORKSPACE, "edl_slot_merge_unique: workspace %zu < required %zu",
               workspace_bytes, W.bytes);
-  const int g = (int)std::min<int64_t>(edl_cdiv(cap, kThreads), EDL_SM_COUNT * 8);
+  const int g = (int)std::min<int64_t>(edl_cdiv(cap, kThreads * kMK), EDL_SM_COUNT * 8);
   k_slot_merge<<<g, kThreads, 0, st>>>((const long long*)keys_slots, counts_dev, num_slots, (long long)slot_stride,
                                        (long long)slot_limit, W.sorted, (uint32_t*)order, n_out_dev);
   const int tiles = (int)edl_cdiv(cap, kTile);
