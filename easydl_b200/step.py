@@ -52,7 +52,7 @@ class SparseStep:
         self.launches_per_step = 1 + K.unique_launches(N, self.F, self.key_bits, self.field_bits) + 4
         self.last_n_unique = self.uq.n_unique
         # The lookup does not need the dedup (it gathers by id), so the two can run side by side:
-        # the radix passes are short latency-bound kernels, the gather is one long HBM-bound one.
+        # the dedup works in shared memory (or in L2 for the radix passes), the gather is one long HBM-bound kernel.
         if overlap_dedup is None:
             overlap_dedup = os.environ.get("EDL_STEP_OVERLAP", "1") == "1"
         self.side = torch.cuda.Stream(device=dev, priority=-1) if overlap_dedup else None
@@ -125,7 +125,7 @@ class SparseStep:
 
 class GraphedStep:
     """A SparseStep captured into CUDA graphs for one fixed (ids, grad) buffer pair: the 17
-    launches of a step cost one graph launch instead of 17 trips through the driver.  Three
+    launches of a step cost one graph launch instead of one trip through the driver each.  Three
     graphs (lookup / dedup / update) so that a caller can time the phases with events between
     them, plus one graph of the whole step.  The optimizer rate is read from a device scalar
     (ShardParameters.lr_dev) that run() refreshes before every replay, so Adam's bias-corrected
