@@ -124,7 +124,7 @@ class SparseStep:
 
 
 class GraphedStep:
-    """A SparseStep captured into CUDA graphs for one fixed (ids, grad) buffer pair: the 17
+    """A SparseStep captured into CUDA graphs for one fixed (ids, grad) buffer pair: the
     launches of a step cost one graph launch instead of one trip through the driver each.  Three
     graphs (lookup / dedup / update) so that a caller can time the phases with events between
     them, plus one graph of the whole step.  The optimizer rate is read from a device scalar
