@@ -9,7 +9,8 @@ lookup (A3) -> [upstream gradient, synthetic, resident] -> dedup (A1) -> segment
 Adagrad row update (A4 + A5).  Default workload = BASELINE.json configs[1]: DeepFM-shape,
 26 tables x 10M rows x dim 64, batch 64K, Adagrad, one B200.  For N > 1 the tables are
 row-sharded over the N GPUs (id mod N) and every GPU brings its own 64K batch (weak scaling),
-exchanging ids / rows / gradients by NCCL all-to-all-v.
+exchanging ids / rows / gradients through fixed per-pair slots in peer-mapped buffers over NVLink
+(`--exchange slots`, the default; `peer` and `nccl` are the packed all-to-all-v forms).
 
 One JSON line on stdout (rank 0).  `value` is device-resident throughput; `e2e` is the same
 step through the host-buffer PS API (ids H2D, embeddings D2H, gradients H2D each step).
@@ -349,7 +350,7 @@ def run_b200_arm(a):
         if slots:
             # fixed per-pair slots, no host round trip: the step is replayed from CUDA graphs below
             from easydl_b200.slot_step import PipelinedSlotStep, SlotShardedStep
-            if a.exchange == "slots-pipe":     # table groups one stage apart (not yet timed on real ranks)
+            if a.exchange == "slots-pipe":     # table groups one stage apart (measured slower than `slots`)
                 step = PipelinedSlotStep(params, B, group=dist.group.WORLD, wire_dtype=wire_dtype, n_lanes=a.lanes)
             else:
                 step = SlotShardedStep(params, B, group=dist.group.WORLD, wire_dtype=wire_dtype)
@@ -650,7 +651,7 @@ def run_b200_arm(a):
             line["e2e"] = e2e
         if lineage:
             line["e2e_lineage_api"] = lineage
-        if not a.no_cpu_baseline:
+        if not a.no_cpu_baseline and world == 1:     # the CPU port beside the N = 1 line only
             v, spp = cpu_reference(a, 1, a.cpu_steps, 1)
             line["cpu_baseline"] = {
                 "value": v, "unit": UNIT, "cores": 1, "kind": "port",

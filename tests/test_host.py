@@ -198,6 +198,37 @@ def test_header_is_plain_c_and_c_host_links(tmp_path):
     assert os.path.exists(tmp_path / "c_host")
 
 
+def test_ctypes_prototypes_match_the_header_types():
+    """Every parameter and return type of _lib.PROTOTYPES has the kind (pointer / integer / float) and the
+    width of the C declaration in include/edlsparse.h: a drifted binding would pass garbage to a kernel."""
+    import ctypes as C
+    from easydl_b200 import _lib
+    hdr = open(os.path.join(ROOT, "include", "edlsparse.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    decls = re.findall(r"([A-Za-z_][\w\s\*]*?)\b(edl_[a-z0-9_]+)\s*\(([^)]*)\)\s*;", hdr)
+    scalars = {"int": ("int", C.sizeof(C.c_int)), "int32_t": ("int", 4), "int64_t": ("int", 8), "uint64_t": ("int", 8),
+               "size_t": ("int", C.sizeof(C.c_size_t)), "float": ("float", 4), "edl_stream_t": ("ptr", 8)}
+
+    def c_kind(t):
+        t = re.sub(r"\b(const|unsigned)\b", "", t).strip()
+        return ("ptr", 8) if "*" in t else scalars[t]
+
+    def py_kind(a):
+        if a is None:
+            return None
+        if a in (C.c_void_p, C.c_char_p) or issubclass(a, C._Pointer):
+            return ("ptr", 8)
+        return ("float" if a in (C.c_float, C.c_double) else "int", C.sizeof(a))
+
+    assert len(decls) == len(_lib.PROTOTYPES)
+    for ret, name, args in decls:
+        res, argtypes = _lib.PROTOTYPES[name]
+        want = [c_kind(re.match(r"(.*?)\w+$", x.strip()).group(1)) for x in args.split(",") if x.strip() not in ("", "void")]
+        assert [py_kind(x) for x in argtypes] == want, name
+        assert py_kind(res) == c_kind(ret), name
+    assert C.sizeof(_lib.OptParams) == 32       # edl_opt_params: int + 4 floats, padded, then a pointer
+
+
 def _touch_version(d, v, shards, S):
     import os
     os.makedirs(os.path.join(d, f"version-{v}"), exist_ok=True)
