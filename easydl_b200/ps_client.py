@@ -147,7 +147,10 @@ class PSClient:
         return emb.cpu().numpy().reshape(B, F, -1)
 
     def push_gradient_batch(self, grads):
-        """grads: host [B, F, dim], gradient of the last pull_embedding_batch's output."""
+        """grads: host [B, F, dim], gradient of the last pull_embedding_batch's output.
+        One in-process shard (S == 1): the call returns once the upload and the update are ENQUEUED.  A pageable
+        array has been read by then; a PINNED array is read by the copy engine later, so leave it unchanged until
+        the next pull_embedding_batch returns (its wait covers this upload) or the device is synchronised."""
         from . import kernels as K
         if self._last == "fast":
             return self._push_batch_fast(torch.as_tensor(grads, dtype=torch.float32))
