@@ -51,6 +51,10 @@ def parse_args():
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-steps", type=int, default=3, help="timed oracle steps for cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-compiled-child", type=int, default=0, metavar="THREADS",
+                    help="internal: time the compiled CPU path (oracle/edl_oracle_c.c) on THREADS threads and print one "
+                         "JSON object; bench.py runs this in a child process so that a fault there cannot cost the line")
+    ap.add_argument("--cpu-budget-s", type=float, default=60.0, help="time budget of one CPU baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-prefetch", action="store_true",
                     help="N=1: time only the strictly sequential step (no dedup of the next batch beside the update)")
@@ -224,6 +228,56 @@ def cpu_reference(a, threads: int, steps: int, warmup: int, nb_max: int = 2, sta
     return a.batch * steps / dt, dt / steps
 
 
+def cpu_compiled_child(a):
+    """Child process: the compiled CPU parameter-server path (oracle/edl_oracle_c.c: one table per thread, a hash
+    map id -> row per table) on the same workload.  Honours --steps / --warmup up to --cpu-budget-s."""
+    from oracle import edl_oracle as O
+    from oracle import edl_oracle_c as OC
+    threads = max(1, a.cpu_compiled_child)
+    rows = [a.rows] * N_FIELDS
+    opt = O.OptimizerSpec.adagrad() if a.optimizer == "adagrad" else O.OptimizerSpec.adam()
+    shard = OC.CShard(rows, a.dim, opt)
+    nb = max(1, a.n_batches)
+    batches = [O.criteo_batch(rows, a.batch, a.alpha, step=i)[1] for i in range(nb)]
+    grad = O.synthetic_grad(a.batch * N_FIELDS, a.dim)
+    emb = None
+    t0 = time.perf_counter()
+    for ids in batches:                     # untimed: materialises the rows of every batch
+        shard.sparse_step(ids, grad, threads=threads, want_emb=False)
+    probe = (time.perf_counter() - t0) / nb
+    steps = max(1, min(a.steps, int(a.cpu_budget_s / max(probe, 1e-3))))
+    warm = max(0, min(a.warmup, int(0.2 * a.cpu_budget_s / max(probe, 1e-3))))
+    for i in range(warm):
+        shard.sparse_step(batches[i % nb], grad, threads=threads)
+    n_u = []
+    t0 = time.perf_counter()
+    for i in range(steps):
+        emb, u = shard.sparse_step(batches[(warm + i) % nb], grad, threads=threads)
+        n_u.append(u)
+    dt = time.perf_counter() - t0
+    del emb
+    print(json.dumps({"value": a.batch * steps / dt, "ms_per_step": dt / steps * 1e3, "steps": steps, "warmup": warm,
+                      "threads": threads, "nb": nb, "unique_per_step": float(np.mean(n_u))}), flush=True)
+
+
+def cpu_compiled(a, threads, steps, warmup, budget_s, timeout_s=420):
+    """Run cpu_compiled_child in a child process -> its JSON object, or None (library not built, fault, time-out)."""
+    import subprocess
+    if not os.path.exists(os.path.join(ROOT, "oracle", "libedloracle.so")):
+        return None
+    cmd = [sys.executable, os.path.abspath(__file__), "--cpu-compiled-child", str(threads), "--steps", str(steps),
+           "--warmup", str(warmup), "--rows", str(a.rows), "--dim", str(a.dim), "--batch", str(a.batch),
+           "--alpha", str(a.alpha), "--optimizer", a.optimizer, "--n-batches", str(a.n_batches),
+           "--cpu-budget-s", str(budget_s)]
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout_s)
+        if r.returncode != 0:
+            return None
+        return json.loads(r.stdout.strip().splitlines()[-1])
+    except Exception:
+        return None
+
+
 def config_for(a, world, U_mean=None, nb=None):
     """The `config` object of the JSON line: the WORKLOAD only, so that both arms print the same object
     (how an arm runs it goes into `implementation`)."""
@@ -241,31 +295,50 @@ def config_for(a, world, U_mean=None, nb=None):
 
 
 def run_reference_arm(a):
+    """The CPU parameter-server path on the host cores, all threads.  Primary leg: the compiled restatement
+    (oracle/edl_oracle_c.c, in a child process); the NumPy oracle port is timed beside it on a short sample and is
+    the primary leg when the C library is not built or its child fails."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     cores = os.cpu_count() or 1
     threads = min(cores, N_FIELDS)
-    # honour --steps / --warmup as far as a bounded run allows: one probe step sizes the run to ~150 s
+    c = cpu_compiled(a, threads, a.steps, a.warmup, budget_s=90.0)
+    # NumPy port: one probe step sizes the run (30 s beside the compiled leg, 150 s when it is the only one)
     probe_v, probe_spp = cpu_reference(a, threads, 1, 1)
-    budget_s = 150.0
+    budget_s = 30.0 if c else 150.0
     steps = max(1, min(a.steps, int(budget_s / max(probe_spp, 1e-3))))
     warm = max(0, min(a.warmup, int(0.2 * budget_s / max(probe_spp, 1e-3))))
     st = {}
     v, spp = cpu_reference(a, threads, steps, warm, nb_max=a.n_batches, state=st)
-    sample = (f"{steps} full steps (batch {a.batch}, {N_FIELDS} tables, dim {a.dim}) of the NumPy oracle, "
-              f"one table per thread on {threads} threads, rows pre-materialised")
-    cfg = config_for(a, a.gpus, st["U_of"](warm, steps), st["nb"])
+    numpy_leg = {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "ms_per_step": spp * 1e3,
+                 "sample": f"{steps} full steps (batch {a.batch}, {N_FIELDS} tables, dim {a.dim}) of the NumPy oracle, "
+                           f"one table per thread on {threads} threads, rows pre-materialised"}
+    if c:
+        value, ms, k_steps, k_warm = c["value"], c["ms_per_step"], c["steps"], c["warmup"]
+        cfg = config_for(a, a.gpus, c["unique_per_step"], c["nb"])
+        primary = {"value": value, "unit": UNIT, "cores": c["threads"], "kind": "port", "ms_per_step": ms,
+                   "sample": f"{k_steps} full steps (batch {a.batch}, {N_FIELDS} tables, dim {a.dim}) of the compiled C "
+                             f"restatement (oracle/edl_oracle_c.c: hash map id -> row per table, gcc -O3, SSE2 / AVX2), "
+                             f"one table per thread on {c['threads']} threads, rows pre-materialised"}
+        path = "CPU parameter-server path (compiled C port of the oracle), one host, all cores; the GPUs are unused"
+    else:
+        value, ms, k_steps, k_warm = v, spp * 1e3, steps, warm
+        cfg = config_for(a, a.gpus, st["U_of"](warm, steps), st["nb"])
+        primary = numpy_leg
+        path = "CPU parameter-server path (NumPy oracle port), one host, all cores; the GPUs are unused"
     line = {
-        "metric": METRIC, "value": v, "unit": UNIT, "impl": "reference", "n_gpus": a.gpus,
-        "steps": steps, "warmup": warm, "ms_per_step": spp * 1e3, "higher_is_better": True,
+        "metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": a.gpus,
+        "steps": k_steps, "warmup": k_warm, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": cfg,
-        "implementation": {"code_path": "CPU parameter-server path (oracle port), one host, all cores; the GPUs are unused"},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
-        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "implementation": {"code_path": path},
+        "cpu_baseline": primary,
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if c:
+        line["cpu_baseline_numpy"] = numpy_leg
     print(json.dumps(line), flush=True)
 
 
@@ -658,6 +731,13 @@ def run_b200_arm(a):
                 "sample": f"{a.cpu_steps} full steps of the same workload through the NumPy oracle "
                           f"(1 thread; {os.cpu_count()} cores present), rows pre-materialised",
                 "ms_per_step": spp * 1e3}
+            cores = os.cpu_count() or 1
+            c = cpu_compiled(a, min(cores, N_FIELDS), 20, 2, budget_s=20.0, timeout_s=240)
+            if c:
+                line["cpu_baseline_compiled"] = {
+                    "value": c["value"], "unit": UNIT, "cores": c["threads"], "kind": "port", "ms_per_step": c["ms_per_step"],
+                    "sample": f"{c['steps']} full steps of the same workload through the compiled C restatement "
+                              f"(oracle/edl_oracle_c.c), one table per thread on {c['threads']} threads, rows pre-materialised"}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -665,7 +745,9 @@ def run_b200_arm(a):
 
 def main():
     a = parse_args()
-    if a.impl == "reference":
+    if a.cpu_compiled_child:
+        cpu_compiled_child(a)
+    elif a.impl == "reference":
         run_reference_arm(a)
     else:
         run_b200_arm(a)
