@@ -284,3 +284,26 @@ def test_unique_launch_count_follows_the_dedup_path():
         assert K.unique_launches(32768 * 26, 26, 30, 26) == 15         # no pass saved: flat sort
     finally:
         _lib.tuning_set("dedup_impl", saved)
+
+
+def test_reference_arm_prints_the_contract_line():
+    """bench.py --impl reference on a small workload (no GPU): one JSON line with the contract's keys, the compiled
+    CPU path as the primary leg and the NumPy port beside it, both counting the same unique ids per step."""
+    import json, subprocess, sys
+    subprocess.run(["make", "-C", os.path.join(ROOT, "oracle")], check=True, capture_output=True)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--rows", "20000",
+                        "--batch", "512", "--dim", "16", "--steps", "3", "--warmup", "1", "--n-batches", "2"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    for k in ("metric", "value", "unit", "impl", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better",
+              "scaling", "dtype", "data", "config", "cpu_baseline", "e2e"):
+        assert k in line, k
+    assert line["impl"] == "reference" and line["steps"] == 3 and line["warmup"] == 1 and line["gpu_launches"] == 0
+    assert line["e2e"] == {"value": line["value"], "unit": line["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert "compiled C" in line["cpu_baseline"]["sample"] and line["cpu_baseline"]["value"] == line["value"]
+    assert "NumPy" in line["cpu_baseline_numpy"]["sample"] and line["cpu_baseline_numpy"]["value"] > 0
+    # the same batches, so the same unique ids per step as the NumPy oracle counts
+    rows = [20000] * 26
+    u = [len(np.unique(O.fuse_keys(O.criteo_batch(rows, 512, 1.05, step=i)[1], O.key_bases(rows)))) for i in range(2)]
+    assert line["config"]["unique_per_step"] == round(float(np.mean([u[(1 + i) % 2] for i in range(3)])), 1)
