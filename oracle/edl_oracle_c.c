@@ -20,6 +20,7 @@
 #include <math.h>
 #include <pthread.h>
 #include <stdint.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -420,4 +421,46 @@ void edlo_shard_export(const void* p, int64_t* keys_out, float* w_out, float* s0
     }
     base += sh->rows[t];
   }
+}
+
+/* ------------------------------------------------------------------ SPEC 'A6 re-shard', 'Checkpoint file'
+ * Writes the file shard `new_shard` of `new_S` would hold after a re-shard of this (single) shard: the
+ * materialised records with id mod new_S == new_shard, per table, ids ascending.  Little-endian:
+ * "EDLS", version u32, S u32, shard u32, T u32, step u64, optimizer u32; per table t u32, D u32, n u64,
+ * ids[n] i64, rows[n * D] f32, slot0[n * D] f32 (, slot1[n * D] f32 for Adam).  -> 0, or -1 on an I/O error. */
+static int put(FILE* f, const void* p, size_t n) { return n == 0 || fwrite(p, 1, n, f) == n; }
+
+int edlo_shard_write_checkpoint(const void* p, const char* path, int new_S, int new_shard) {
+  const edlo_shard* sh = (const edlo_shard*)p;
+  const int dim = sh->dim;
+  FILE* f = fopen(path, "wb");
+  if (!f) return -1;
+  const uint32_t head[4] = {1u, (uint32_t)new_S, (uint32_t)new_shard, (uint32_t)sh->T};
+  const uint64_t step = (uint64_t)sh->step;
+  const uint32_t kind = (uint32_t)sh->kind;
+  int ok = put(f, "EDLS", 4) && put(f, head, sizeof head) && put(f, &step, 8) && put(f, &kind, 4);
+  for (int t = 0; t < sh->T && ok; ++t) {
+    const edlo_table* tb = &sh->tab[t];
+    const int64_t n = tb->n;
+    int64_t* uniq = (int64_t*)malloc((size_t)(n + 1) * 8);
+    int32_t* inverse = (int32_t*)malloc((size_t)(n + 1) * 4);
+    int32_t* counts = (int32_t*)malloc((size_t)(n + 1) * 4);
+    int32_t* order = (int32_t*)malloc((size_t)(n + 1) * 4);
+    int32_t* seg = (int32_t*)malloc((size_t)(n + 2) * 4);
+    edlo_dedup(tb->ids, n, uniq, inverse, counts, order, seg); /* order = rows by ascending id */
+    uint64_t m = 0;
+    for (int64_t i = 0; i < n; ++i) m += (tb->ids[order[i]] % new_S) == new_shard;
+    const uint32_t th[2] = {(uint32_t)t, (uint32_t)dim};
+    ok = ok && put(f, th, sizeof th) && put(f, &m, 8);
+    for (int64_t i = 0; i < n && ok; ++i)
+      if ((tb->ids[order[i]] % new_S) == new_shard) ok = put(f, &tb->ids[order[i]], 8);
+    const float* arrays[3] = {tb->w, tb->s0, sh->kind == EDLO_ADAM ? tb->s1 : NULL};
+    for (int a = 0; a < 3 && ok; ++a) {
+      if (!arrays[a]) continue;
+      for (int64_t i = 0; i < n && ok; ++i)
+        if ((tb->ids[order[i]] % new_S) == new_shard) ok = put(f, arrays[a] + (int64_t)order[i] * dim, (size_t)dim * 4);
+    }
+    free(uniq); free(inverse); free(counts); free(order); free(seg);
+  }
+  return (fclose(f) == 0 && ok) ? 0 : -1;
 }

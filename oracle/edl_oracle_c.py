@@ -32,6 +32,7 @@ _PROTOS = {
     "edlo_shard_rows": (_i64, [_p]),
     "edlo_shard_step": (_i64, [_p, _p, _i64, _int, _p, _p, _int]),
     "edlo_shard_export": (None, [_p, _p, _p, _p, _p]),
+    "edlo_shard_write_checkpoint": (_int, [_p, C.c_char_p, _int, _int]),
 }
 
 
@@ -150,6 +151,11 @@ class CShard:
         emb = np.empty((B * F, self.dim), dtype=np.float32) if want_emb else None
         n_u = self.lib.edlo_shard_step(self.h, _ptr(ids), B, F, _ptr(grad), _ptr(emb), int(threads))
         return emb, int(n_u)
+
+    def write_checkpoint(self, path: str, new_S: int = 1, new_shard: int = 0):
+        """The EDLS file of shard `new_shard` of `new_S` after a re-shard of this shard (SPEC A6 + file format)."""
+        if self.lib.edlo_shard_write_checkpoint(self.h, os.fsencode(path), int(new_S), int(new_shard)) != 0:
+            raise OSError(f"could not write {path}")
 
     def export(self):
         """(keys ascending, rows, [slots...], step) like OracleShard.export()."""
